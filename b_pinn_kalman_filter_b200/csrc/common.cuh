@@ -1,0 +1,120 @@
+// Shared device/host helpers for the sm_100a kernels of the PC-sampling hot path.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+#define B200_OK 0
+#define B200_ERR_ARG (-1)
+#define B200_ERR_UNSUPPORTED (-2)
+#define B200_ERR_DRIVER (-3)
+
+// Every launcher returns B200_OK or -(1000 + cudaError) so the host side can raise.
+#define B200_RETURN_LAST()                                        \
+  do {                                                            \
+    cudaError_t e__ = cudaGetLastError();                         \
+    return e__ == cudaSuccess ? B200_OK : -(1000 + (int)e__);     \
+  } while (0)
+
+#define B200_DT_F32 0
+#define B200_DT_BF16 1
+
+#define B200_NUM_SMS 148
+
+namespace b200 {
+
+typedef __nv_bfloat16 bf16;
+
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(bf16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ float silu(float v) { return v / (1.0f + __expf(-v)); }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Block-wide sum; every thread gets the result.  `red` is >= 32 floats of shared memory.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int nw = (blockDim.x + 31) >> 5;
+  v = warp_sum(v);
+  __syncthreads();
+  if (lane == 0) red[wid] = v;
+  __syncthreads();
+  float r = (lane < nw) ? red[lane] : 0.0f;
+  r = warp_sum(r);
+  return r;
+}
+
+// 8-wide vector of T (16 B for bf16, 32 B for fp32) as floats.
+template <typename T> struct Vec8;
+template <> struct Vec8<float> {
+  static __device__ __forceinline__ void load(const float* p, float* v) {
+    float4 a = *reinterpret_cast<const float4*>(p);
+    float4 b = *reinterpret_cast<const float4*>(p + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+  static __device__ __forceinline__ void store(float* p, const float* v) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+  }
+};
+template <> struct Vec8<bf16> {
+  static __device__ __forceinline__ void load(const bf16* p, float* v) {
+    uint4 r = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 f = __bfloat1622float2(h[i]);
+      v[2 * i] = f.x; v[2 * i + 1] = f.y;
+    }
+  }
+  static __device__ __forceinline__ void store(bf16* p, const float* v) {
+    uint4 r;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = r;
+  }
+};
+
+// ---------------- Philox4x32-10 (counter-based RNG for the fused noise path) ----------------
+struct Philox {
+  static __device__ __forceinline__ uint4 round10(uint4 ctr, uint2 key) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+      uint32_t hi0 = __umulhi(M0, ctr.x), lo0 = M0 * ctr.x;
+      uint32_t hi1 = __umulhi(M1, ctr.z), lo1 = M1 * ctr.z;
+      ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+      key.x += W0; key.y += W1;
+    }
+    return ctr;
+  }
+  // Four N(0,1) variates for (seed, stream offset, index of the 4-element group).
+  static __device__ __forceinline__ float4 normal4(uint64_t seed, uint64_t offset, uint64_t group) {
+    uint4 c = make_uint4((uint32_t)group, (uint32_t)(group >> 32), (uint32_t)offset, (uint32_t)(offset >> 32));
+    uint2 k = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+    uint4 r = round10(c, k);
+    // Box-Muller on (0,1] uniforms.
+    const float S = 2.3283064365386963e-10f;  // 2^-32
+    float u0 = ((float)r.x + 1.0f) * S, u1 = (float)r.y * S;
+    float u2 = ((float)r.z + 1.0f) * S, u3 = (float)r.w * S;
+    u0 = fminf(u0, 1.0f); u2 = fminf(u2, 1.0f);
+    float ra = sqrtf(-2.0f * __logf(u0)), rb = sqrtf(-2.0f * __logf(u2));
+    float sa, ca, sb, cb;
+    __sincosf(6.283185307179586f * u1, &sa, &ca);
+    __sincosf(6.283185307179586f * u3, &sb, &cb);
+    return make_float4(ra * ca, ra * sa, rb * cb, rb * sb);
+  }
+};
+
+static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+}  // namespace b200

@@ -1,0 +1,167 @@
+// GroupNorm (+ optional SiLU) on channels-last activations for sm_100a, split into
+//   gn_partial : per-(sample, split, group) sum / sum-of-squares   (reads x once: 1 pass, warp/shared reductions)
+//   gn_apply   : y = act((x - mean) * rstd * gamma + beta)          (reads x, writes y; folds the partials itself)
+// Replaces torch's nn.GroupNorm(num_groups=min(C//4,32), eps=1e-6) + SiLU pairs of the score networks
+// (models/layerspp.py:219,231,243,264; models/layers.py:618-642; models/ncsnpp.py:194-228).
+// Both kernels accept TWO sources concatenated along C, so the skip-connection `torch.cat([h, hs.pop()], 1)`
+// (models/ncsnpp.py:318) is never materialised before normalisation.
+// HBM-bound: stats 1 read, apply 1 read + 1 write of the activation (2 B/elem bf16, 4 B/elem fp32).
+#include "common.cuh"
+#include "../../include/b200_sde.h"
+
+namespace b200 {
+
+struct GnArgs {
+  const void* x1; const void* x2; int C1, C2;   // sources [B, HW, C1] and [B, HW, C2] (x2 may be null, C2 = 0)
+  int B, HW, G, nsplit;
+  float* partial;                               // [B, nsplit, G, 2]
+  const float* gamma; const float* beta; float eps; int act;  // act: 0 none, 1 silu
+  void* out;                                    // [B, HW, C1+C2]
+};
+
+// Thread layout shared by both kernels: `nthr` threads sweep pixels; nthr is a multiple of CV = C/8 so that each
+// thread always owns the same 8 channels (cv = tid % CV) and steps over pixels.
+template <typename T>
+__global__ void __launch_bounds__(256) gn_partial_kernel(GnArgs a) {
+  extern __shared__ float sh[];  // [C] sums, [C] sumsq
+  const int C = a.C1 + a.C2, CV = C >> 3;
+  const int b = blockIdx.x / a.nsplit, sp = blockIdx.x % a.nsplit;
+  const int ppt = blockDim.x / CV;              // pixels per sweep
+  const int cv = threadIdx.x % CV, pl = threadIdx.x / CV;
+  const int c0 = cv << 3;
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.0f;
+  __syncthreads();
+  const int per = (a.HW + a.nsplit - 1) / a.nsplit;
+  const int p_begin = sp * per, p_end = min(a.HW, p_begin + per);
+  const T* src; int cs, cc;
+  if (c0 < a.C1) { src = (const T*)a.x1; cs = a.C1; cc = c0; } else { src = (const T*)a.x2; cs = a.C2; cc = c0 - a.C1; }
+  src += (size_t)b * a.HW * cs + cc;
+  float s[8], q[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s[j] = 0.f; q[j] = 0.f; }
+  for (int p = p_begin + pl; p < p_end; p += ppt) {
+    float v[8];
+    Vec8<T>::load(src + (size_t)p * cs, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j] += v[j]; q[j] = fmaf(v[j], v[j], q[j]); }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { atomicAdd(&sh[c0 + j], s[j]); atomicAdd(&sh[C + c0 + j], q[j]); }
+  __syncthreads();
+  const int cpg = C / a.G;
+  for (int g = threadIdx.x; g < a.G; g += blockDim.x) {
+    float ts = 0.f, tq = 0.f;
+    for (int j = 0; j < cpg; ++j) { ts += sh[g * cpg + j]; tq += sh[C + g * cpg + j]; }
+    float* o = a.partial + (((size_t)b * a.nsplit + sp) * a.G + g) * 2;
+    o[0] = ts; o[1] = tq;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) gn_apply_kernel(GnArgs a) {
+  extern __shared__ float sh[];  // [G] mean, [G] rstd
+  const int C = a.C1 + a.C2, CV = C >> 3;
+  const int b = blockIdx.x / a.nsplit, sp = blockIdx.x % a.nsplit;
+  const int cpg = C / a.G;
+  for (int g = threadIdx.x; g < a.G; g += blockDim.x) {
+    double ts = 0.0, tq = 0.0;
+    for (int k = 0; k < a.nsplit; ++k) {
+      const float* o = a.partial + (((size_t)b * a.nsplit + k) * a.G + g) * 2;
+      ts += (double)o[0]; tq += (double)o[1];
+    }
+    const double n = (double)a.HW * cpg;
+    const double mean = ts / n;
+    double var = tq / n - mean * mean;
+    if (var < 0.0) var = 0.0;
+    sh[g] = (float)mean;
+    sh[a.G + g] = (float)(1.0 / sqrt(var + (double)a.eps));
+  }
+  __syncthreads();
+  const int ppt = blockDim.x / CV;
+  const int cv = threadIdx.x % CV, pl = threadIdx.x / CV;
+  const int c0 = cv << 3;
+  float sc[8], sf[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = c0 + j, g = c / cpg;
+    const float ga = a.gamma ? a.gamma[c] : 1.0f, be = a.beta ? a.beta[c] : 0.0f;
+    sc[j] = sh[a.G + g] * ga;
+    sf[j] = be - sh[g] * sc[j];
+  }
+  const int per = (a.HW + a.nsplit - 1) / a.nsplit;
+  const int p_begin = sp * per, p_end = min(a.HW, p_begin + per);
+  const T* src; int cs, cc;
+  if (c0 < a.C1) { src = (const T*)a.x1; cs = a.C1; cc = c0; } else { src = (const T*)a.x2; cs = a.C2; cc = c0 - a.C1; }
+  src += (size_t)b * a.HW * cs + cc;
+  T* dst = (T*)a.out + (size_t)b * a.HW * C + c0;
+  for (int p = p_begin + pl; p < p_end; p += ppt) {
+    float v[8];
+    Vec8<T>::load(src + (size_t)p * cs, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float y = fmaf(v[j], sc[j], sf[j]);
+      v[j] = a.act ? silu(y) : y;
+    }
+    Vec8<T>::store(dst + (size_t)p * C, v);
+  }
+}
+
+static int gn_threads(int C) {
+  const int CV = C / 8;
+  if (CV <= 0 || CV > 256) return 0;
+  return (256 / CV) * CV;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_gn_nsplit(int B, int HW) {
+  // enough blocks to fill 148 SMs a few times over, but never fewer than 64 pixels per block
+  int want = (B200_NUM_SMS * 4 + B - 1) / (B > 0 ? B : 1);
+  int maxs = HW / 64 > 0 ? HW / 64 : 1;
+  int s = want < maxs ? want : maxs;
+  if (s < 1) s = 1;
+  if (s > 32) s = 32;
+  return s;
+}
+
+static int gn_fill(GnArgs& a, const void* x1, int C1, const void* x2, int C2, int B, int HW, int G, int nsplit,
+                   float* partial) {
+  const int C = C1 + C2;
+  if (!x1 || !partial || B < 0 || HW <= 0 || G <= 0 || nsplit <= 0 || C1 <= 0 || C2 < 0 || (C2 > 0 && !x2)) return B200_ERR_ARG;
+  if (C1 % 8 || C2 % 8 || C % G || gn_threads(C) == 0) return B200_ERR_UNSUPPORTED;
+  a.x1 = x1; a.x2 = x2; a.C1 = C1; a.C2 = C2; a.B = B; a.HW = HW; a.G = G; a.nsplit = nsplit; a.partial = partial;
+  a.gamma = nullptr; a.beta = nullptr; a.eps = 0.f; a.act = 0; a.out = nullptr;
+  return B200_OK;
+}
+
+extern "C" int b200_gn_partial(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G,
+                               int nsplit, float* partial, cudaStream_t st) {
+  GnArgs a;
+  int rc = gn_fill(a, x1, C1, x2, C2, B, HW, G, nsplit, partial);
+  if (rc || B == 0) return rc;
+  const int C = C1 + C2, thr = gn_threads(C);
+  const size_t smem = 2 * C * sizeof(float);
+  if (dtype == B200_DT_F32) gn_partial_kernel<float><<<B * nsplit, thr, smem, st>>>(a);
+  else if (dtype == B200_DT_BF16) gn_partial_kernel<bf16><<<B * nsplit, thr, smem, st>>>(a);
+  else return B200_ERR_ARG;
+  B200_RETURN_LAST();
+}
+
+extern "C" int b200_gn_apply(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G,
+                             int nsplit, const float* partial, const float* gamma, const float* beta, float eps,
+                             int act, void* out, cudaStream_t st) {
+  GnArgs a;
+  int rc = gn_fill(a, x1, C1, x2, C2, B, HW, G, nsplit, const_cast<float*>(partial));
+  if (rc) return rc;
+  if (!out) return B200_ERR_ARG;
+  if (B == 0) return B200_OK;
+  a.gamma = gamma; a.beta = beta; a.eps = eps; a.act = act; a.out = out;
+  const int C = C1 + C2, thr = gn_threads(C);
+  const size_t smem = 2 * G * sizeof(float);
+  if (dtype == B200_DT_F32) gn_apply_kernel<float><<<B * nsplit, thr, smem, st>>>(a);
+  else if (dtype == B200_DT_BF16) gn_apply_kernel<bf16><<<B * nsplit, thr, smem, st>>>(a);
+  else return B200_ERR_ARG;
+  B200_RETURN_LAST();
+}

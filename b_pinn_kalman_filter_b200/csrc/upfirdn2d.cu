@@ -1,0 +1,256 @@
+// upfirdn2d for sm_100a: zero-insert upsample x`up`, pad, 2-D FIR with the flipped filter, decimate x`down`.
+// Replaces op/upfirdn2d_kernel.cu:49-207 (+ host dispatch :209-368) of the reference.
+//
+// out[p, oy, ox] = sum_{ky,kx} U[oy*down + ky, ox*down + kx] * k[kh-1-ky, kw-1-kx]
+// U = in upsampled by zero insertion and shifted by (pad_y0, pad_x0); zero outside.
+// Negative pads crop, exactly like the index arithmetic of the reference kernel.
+//
+// Two data layouts:
+//   * planes  : [n_planes, H, W] fp32 (the NCHW view `input.reshape(-1, H, W, 1)` of op/upfirdn2d.py:99) -- op API.
+//   * nhwc    : [B, H, W, C] fp32/bf16 channels-last, 8 channels per thread -- used inside the score engine.
+// Both are HBM-bound: algorithmic bytes = 4*(in_elems + out_elems) (planes).
+#include "common.cuh"
+#include "../../include/b200_sde.h"
+
+namespace b200 {
+
+__host__ __device__ __forceinline__ int floor_div(int a, int b) {
+  int q = a / b, r = a % b;
+  return (r != 0 && ((r < 0) != (b < 0))) ? q - 1 : q;
+}
+__host__ __device__ __forceinline__ int pmod(int a, int b) {
+  int r = a % b;
+  return r < 0 ? r + b : r;
+}
+
+struct UfdTile {
+  int planes, in_h, in_w, out_h, out_w, pad_x0, pad_y0;
+  int toh, tow, ppb, tiles_x, tiles_y, tih, tiw;  // tih/tiw: smem tile extents (upper bounds)
+};
+
+// Shared-memory tiled kernel.  One block = `ppb` consecutive planes x (toh x tow) outputs.
+template <int UP, int DOWN, int KH, int KW>
+__global__ void __launch_bounds__(256) upfirdn2d_planes_kernel(const float* __restrict__ in, const float* __restrict__ k,
+                                                               float* __restrict__ out, UfdTile t) {
+  extern __shared__ float sx[];
+  __shared__ float4 swt[4];  // UP==2: taps regrouped by output parity class (ky0, kx0)
+  // flipped taps in registers: w[ky][kx] = k[KH-1-ky][KW-1-kx]
+  float w[KH][KW];
+#pragma unroll
+  for (int a = 0; a < KH; ++a)
+#pragma unroll
+    for (int b = 0; b < KW; ++b) w[a][b] = __ldg(k + (KH - 1 - a) * KW + (KW - 1 - b));
+  if (UP == 2 && threadIdx.x < 4) {
+    const int ky0 = threadIdx.x >> 1, kx0 = threadIdx.x & 1;
+    auto tap = [&](int ky, int kx) { return __ldg(k + (KH - 1 - ky) * KW + (KW - 1 - kx)); };
+    swt[threadIdx.x] = make_float4(tap(ky0, kx0), tap(ky0, kx0 + 2), tap(ky0 + 2, kx0), tap(ky0 + 2, kx0 + 2));
+  }
+
+  int bid = blockIdx.x;
+  const int tx = bid % t.tiles_x; bid /= t.tiles_x;
+  const int ty = bid % t.tiles_y; bid /= t.tiles_y;
+  const int p0 = bid * t.ppb;
+  const int np = min(t.ppb, t.planes - p0);
+  const int ox0 = tx * t.tow, oy0 = ty * t.toh;
+  const int tow = min(t.tow, t.out_w - ox0), toh = min(t.toh, t.out_h - oy0);
+
+  // input window needed by this tile
+  const int ix0 = floor_div(ox0 * DOWN - t.pad_x0 + UP - 1, UP);
+  const int iy0 = floor_div(oy0 * DOWN - t.pad_y0 + UP - 1, UP);
+  // UP==1, DOWN==2: ix0 + pad_x0 = 2*ox0 is even, so (ox*2 - pad_x0 - ix0) is even -> 8-byte smem reads.
+  const int tiw = t.tiw, tih = t.tih;
+
+  // stage: coalesced along x, zero fill outside the image
+  const int per_plane = tih * tiw;
+  for (int i = threadIdx.x; i < np * per_plane; i += blockDim.x) {
+    int pl = i / per_plane, r = i - pl * per_plane;
+    int yy = r / tiw, xx = r - yy * tiw;
+    int iy = iy0 + yy, ix = ix0 + xx;
+    float v = 0.0f;
+    if (iy >= 0 && iy < t.in_h && ix >= 0 && ix < t.in_w)
+      v = __ldg(in + ((size_t)(p0 + pl) * t.in_h + iy) * t.in_w + ix);
+    sx[i] = v;
+  }
+  __syncthreads();
+
+  const int per_out = toh * tow;
+  for (int i = threadIdx.x; i < np * per_out; i += blockDim.x) {
+    int pl = i / per_out, r = i - pl * per_out;
+    int oyl = r / tow, oxl = r - oyl * tow;
+    int oy = oy0 + oyl, ox = ox0 + oxl;
+    const float* sp = sx + pl * per_plane;
+    float acc = 0.0f;
+    if (UP == 1 && DOWN == 2 && KW == 4) {
+      const int cx = ox * 2 - t.pad_x0 - ix0;  // even by construction
+      const int cy = oy * 2 - t.pad_y0 - iy0;
+#pragma unroll
+      for (int ky = 0; ky < KH; ++ky) {
+        const float2* row = reinterpret_cast<const float2*>(sp + (cy + ky) * tiw + cx);
+        float2 a = row[0], b = row[1];
+        acc = fmaf(a.x, w[ky][0], acc); acc = fmaf(a.y, w[ky][1], acc);
+        acc = fmaf(b.x, w[ky][2], acc); acc = fmaf(b.y, w[ky][3], acc);
+      }
+    } else if (UP == 2) {
+      // two taps per axis; which two depends on the parity of (pad - o)
+      const int ky0 = (t.pad_y0 - oy) & 1, kx0 = (t.pad_x0 - ox) & 1;
+      const float4 wq = swt[ky0 * 2 + kx0];
+      const int yy = ((oy + ky0 - t.pad_y0) >> 1) - iy0, xx = ((ox + kx0 - t.pad_x0) >> 1) - ix0;
+      const float* r0 = sp + yy * tiw + xx;
+      acc = r0[0] * wq.x;
+      acc = fmaf(r0[1], wq.y, acc);
+      acc = fmaf(r0[tiw], wq.z, acc);
+      acc = fmaf(r0[tiw + 1], wq.w, acc);
+    } else {
+      const int cx = ox * DOWN - t.pad_x0 - ix0, cy = oy * DOWN - t.pad_y0 - iy0;
+#pragma unroll
+      for (int ky = 0; ky < KH; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < KW; ++kx) acc = fmaf(sp[(cy + ky) * tiw + cx + kx], w[ky][kx], acc);
+    }
+    out[((size_t)(p0 + pl) * t.out_h + oy) * t.out_w + ox] = acc;
+  }
+}
+
+// Generic fallback: any up/down/filter size, one output per thread, taps straight from global/L1.
+__global__ void upfirdn2d_planes_generic_kernel(const float* __restrict__ in, const float* __restrict__ k,
+                                                float* __restrict__ out, long long total, int in_h, int in_w,
+                                                int out_h, int out_w, int kh, int kw, int up_x, int up_y,
+                                                int down_x, int down_y, int pad_x0, int pad_y0) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    int ox = (int)(i % out_w);
+    long long r = i / out_w;
+    int oy = (int)(r % out_h);
+    long long p = r / out_h;
+    const float* ip = in + p * (long long)in_h * in_w;
+    float acc = 0.0f;
+    for (int ky = pmod(pad_y0 - oy * down_y, up_y); ky < kh; ky += up_y) {
+      int iy = (oy * down_y + ky - pad_y0) / up_y;
+      if (iy < 0 || iy >= in_h) continue;
+      for (int kx = pmod(pad_x0 - ox * down_x, up_x); kx < kw; kx += up_x) {
+        int ix = (ox * down_x + kx - pad_x0) / up_x;
+        if (ix < 0 || ix >= in_w) continue;
+        acc = fmaf(__ldg(ip + (long long)iy * in_w + ix), __ldg(k + (kh - 1 - ky) * kw + (kw - 1 - kx)), acc);
+      }
+    }
+    out[i] = acc;
+  }
+}
+
+// Channels-last variant: one thread = 8 channels of one output pixel.
+template <typename T>
+__global__ void __launch_bounds__(256) upfirdn2d_nhwc_kernel(const T* __restrict__ in, const float* __restrict__ k,
+                                                             T* __restrict__ out, long long total_vec, int C8, int in_h,
+                                                             int in_w, int out_h, int out_w, int kh, int kw, int up,
+                                                             int down, int pad_x0, int pad_y0) {
+  __shared__ float sk[64];
+  if (threadIdx.x < kh * kw) {
+    int ky = threadIdx.x / kw, kx = threadIdx.x % kw;
+    sk[threadIdx.x] = k[(kh - 1 - ky) * kw + (kw - 1 - kx)];
+  }
+  __syncthreads();
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total_vec; i += (long long)gridDim.x * blockDim.x) {
+    int c8 = (int)(i % C8);
+    long long r = i / C8;
+    int ox = (int)(r % out_w); r /= out_w;
+    int oy = (int)(r % out_h);
+    long long b = r / out_h;
+    const T* ip = in + b * (long long)in_h * in_w * C8 * 8 + c8 * 8;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+    for (int ky = pmod(pad_y0 - oy * down, up); ky < kh; ky += up) {
+      int iy = (oy * down + ky - pad_y0) / up;
+      if (iy < 0 || iy >= in_h) continue;
+      for (int kx = pmod(pad_x0 - ox * down, up); kx < kw; kx += up) {
+        int ix = (ox * down + kx - pad_x0) / up;
+        if (ix < 0 || ix >= in_w) continue;
+        float v[8];
+        Vec8<T>::load(ip + ((long long)iy * in_w + ix) * C8 * 8, v);
+        float wk = sk[ky * kw + kx];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(v[j], wk, acc[j]);
+      }
+    }
+    Vec8<T>::store(out + i * 8, acc);
+  }
+}
+
+template <int UP, int DOWN>
+static int launch_tiled(const float* in, const float* k, float* out, int planes, int in_h, int in_w, int out_h,
+                        int out_w, int pad_x0, int pad_y0, cudaStream_t st) {
+  UfdTile t;
+  t.planes = planes; t.in_h = in_h; t.in_w = in_w; t.out_h = out_h; t.out_w = out_w;
+  t.pad_x0 = pad_x0; t.pad_y0 = pad_y0;
+  t.tow = out_w < 64 ? out_w : 64;
+  t.toh = out_h < 32 ? out_h : 32;
+  if (UP == 2) { t.tow = out_w < 128 ? out_w : 128; }
+  t.tiles_x = ceil_div(out_w, t.tow);
+  t.tiles_y = ceil_div(out_h, t.toh);
+  int per = t.toh * t.tow;
+  t.ppb = per >= 1024 ? 1 : (1024 / per);
+  if (t.ppb > planes) t.ppb = planes;
+  t.tiw = ((t.tow - 1) * DOWN + 4 - 1) / UP + 2 + ((UP == 1 && DOWN == 2) ? 1 : 0);
+  if (UP == 1 && DOWN == 2) t.tiw += (t.tiw & 1);
+  t.tih = ((t.toh - 1) * DOWN + 4 - 1) / UP + 2;
+  size_t smem = (size_t)t.ppb * t.tih * t.tiw * sizeof(float);
+  if (smem > 200 * 1024) return B200_ERR_UNSUPPORTED;
+  auto kern = upfirdn2d_planes_kernel<UP, DOWN, 4, 4>;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  long long nblk = (long long)ceil_div(planes, t.ppb) * t.tiles_x * t.tiles_y;
+  if (nblk > 0x7fffffffLL) return B200_ERR_UNSUPPORTED;
+  kern<<<(unsigned)nblk, 256, smem, st>>>(in, k, out, t);
+  B200_RETURN_LAST();
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_upfirdn2d_out_size(int in_size, int k, int up, int down, int pad0, int pad1) {
+  return (in_size * up + pad0 + pad1 - k) / down + 1;
+}
+
+extern "C" int b200_upfirdn2d_f32(const float* in, const float* k, float* out, int n_planes, int in_h, int in_w, int kh,
+                                  int kw, int up_x, int up_y, int down_x, int down_y, int pad_x0, int pad_x1,
+                                  int pad_y0, int pad_y1, cudaStream_t st) {
+  if (!in || !k || !out || n_planes < 0 || in_h <= 0 || in_w <= 0 || kh <= 0 || kw <= 0 || up_x <= 0 || up_y <= 0 ||
+      down_x <= 0 || down_y <= 0)
+    return B200_ERR_ARG;
+  int out_h = (in_h * up_y + pad_y0 + pad_y1 - kh) / down_y + 1;
+  int out_w = (in_w * up_x + pad_x0 + pad_x1 - kw) / down_x + 1;
+  if (out_h <= 0 || out_w <= 0) return B200_ERR_ARG;
+  if (n_planes == 0) return B200_OK;
+  if (kh == 4 && kw == 4 && up_x == up_y && down_x == down_y) {
+    int rc = B200_ERR_UNSUPPORTED;
+    if (up_x == 1 && down_x == 1) rc = launch_tiled<1, 1>(in, k, out, n_planes, in_h, in_w, out_h, out_w, pad_x0, pad_y0, st);
+    else if (up_x == 2 && down_x == 1) rc = launch_tiled<2, 1>(in, k, out, n_planes, in_h, in_w, out_h, out_w, pad_x0, pad_y0, st);
+    else if (up_x == 1 && down_x == 2) rc = launch_tiled<1, 2>(in, k, out, n_planes, in_h, in_w, out_h, out_w, pad_x0, pad_y0, st);
+    if (rc != B200_ERR_UNSUPPORTED) return rc;
+  }
+  long long total = (long long)n_planes * out_h * out_w;
+  int blocks = (int)((total + 255) / 256 < (long long)B200_NUM_SMS * 16 ? (total + 255) / 256 : (long long)B200_NUM_SMS * 16);
+  upfirdn2d_planes_generic_kernel<<<blocks, 256, 0, st>>>(in, k, out, total, in_h, in_w, out_h, out_w, kh, kw, up_x,
+                                                          up_y, down_x, down_y, pad_x0, pad_y0);
+  B200_RETURN_LAST();
+}
+
+extern "C" int b200_upfirdn2d_nhwc(const void* in, const float* k, void* out, int dtype, int batch, int in_h, int in_w,
+                                   int channels, int kh, int kw, int up, int down, int pad0, int pad1, cudaStream_t st) {
+  if (!in || !k || !out || channels % 8 != 0 || kh * kw > 64 || up <= 0 || down <= 0) return B200_ERR_ARG;
+  int out_h = (in_h * up + pad0 + pad1 - kh) / down + 1;
+  int out_w = (in_w * up + pad0 + pad1 - kw) / down + 1;
+  if (out_h <= 0 || out_w <= 0) return B200_ERR_ARG;
+  long long total = (long long)batch * out_h * out_w * (channels / 8);
+  if (total == 0) return B200_OK;
+  long long want = (total + 255) / 256;
+  int blocks = (int)(want < (long long)B200_NUM_SMS * 32 ? want : (long long)B200_NUM_SMS * 32);
+  if (dtype == B200_DT_F32)
+    upfirdn2d_nhwc_kernel<float><<<blocks, 256, 0, st>>>((const float*)in, k, (float*)out, total, channels / 8, in_h,
+                                                         in_w, out_h, out_w, kh, kw, up, down, pad0, pad0);
+  else if (dtype == B200_DT_BF16)
+    upfirdn2d_nhwc_kernel<bf16><<<blocks, 256, 0, st>>>((const bf16*)in, k, (bf16*)out, total, channels / 8, in_h, in_w,
+                                                        out_h, out_w, kh, kw, up, down, pad0, pad0);
+  else
+    return B200_ERR_ARG;
+  B200_RETURN_LAST();
+}

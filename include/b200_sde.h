@@ -1,0 +1,117 @@
+/*
+ * b200_sde.h -- C ABI of libb200sde.so: the sm_100a (B200) kernels behind the reverse-SDE
+ * predictor-corrector sampling hot path of XDzzzzzZyq/b-pinn-kalman-filter.
+ *
+ * Conventions
+ *   - Plain pointers and sizes only; all pointers are DEVICE pointers unless a name ends in `_host`.
+ *   - The caller owns every buffer; no entry point allocates device memory or synchronises.
+ *   - Every launcher takes the CUDA stream to launch on and returns 0 (B200_OK) or a negative code:
+ *       -1 bad argument, -2 unsupported shape, -3 driver entry point missing, -(1000+cudaError_t) launch failure.
+ *   - dtype: 0 = fp32, 1 = bf16 (activations inside the score engine).  Accumulation is always fp32.
+ *   - Channels-last ("nhwc") tensors are [B, H, W, C] with C contiguous; "planes" tensors are [N*C, H, W].
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the reference repo).
+ */
+#ifndef B200_SDE_H_
+#define B200_SDE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+/* library / build info */
+int b200_abi_version(void);
+const char* b200_build_info(void);
+
+/* ---- upfirdn2d ------------------------------------------------------------------------------
+ * replaces: upfirdn2d_op.upfirdn2d pybind (op/upfirdn2d.cpp:12-23), kernels op/upfirdn2d_kernel.cu:49-207,
+ *           python dispatcher op/upfirdn2d.py:145-156 (CPU restatement there: upfirdn2d_native :159-200). */
+int b200_upfirdn2d_out_size(int in_size, int k, int up, int down, int pad0, int pad1);
+int b200_upfirdn2d_f32(const float* in, const float* k, float* out, int n_planes, int in_h, int in_w, int kh, int kw,
+                       int up_x, int up_y, int down_x, int down_y, int pad_x0, int pad_x1, int pad_y0, int pad_y1,
+                       cudaStream_t stream);
+int b200_upfirdn2d_nhwc(const void* in, const float* k, void* out, int dtype, int batch, int in_h, int in_w,
+                        int channels, int kh, int kw, int up, int down, int pad0, int pad1, cudaStream_t stream);
+
+/* ---- fused bias + activation ----------------------------------------------------------------
+ * replaces: fused.fused_bias_act pybind (op/fused_bias_act.cpp:11-20), kernel op/fused_bias_act_kernel.cu:18-49.
+ * act: 1 linear, 3 leaky-relu; grad: 0 fwd, 1 (uses sign of `ref`), 2 (zeros). bias/ref may be NULL. */
+int b200_fused_bias_act_f32(float* out, const float* x, const float* bias, const float* ref, long long n,
+                            long long step_b, int size_b, int act, int grad, float alpha, float scale,
+                            cudaStream_t stream);
+
+/* ---- Navier-Stokes simulator step -----------------------------------------------------------
+ * replaces: ns_step_forward.update_{density,velocity,pressure} pybind (op/ns_step.cpp:45-107) and the kernels in
+ * op/ns_step_kernel.cu:96-234.  Fields are [B, C, H, W] fp32.  `scratch` (B*2*H*W floats) is only needed when
+ * bug_compat = 1 (reproduces the reference's cross-sample plane mix-up for B > 1, op/ns_step.cpp:70-72). */
+int b200_ns_update_density(float* dens_out, const float* dens, const float* vel, int B, int H, int W, float dt, float dx,
+                           cudaStream_t stream);
+int b200_ns_update_velocity(float* vel_out, const float* vel, const float* pres, float* scratch, int B, int H, int W,
+                            float dt, float dx, int bug_compat, cudaStream_t stream);
+int b200_ns_update_pressure(float* pres_out, const float* pres, const float* vel, int B, int H, int W, float dt,
+                            float dx, cudaStream_t stream);
+/* building blocks: v* = v - dt grad(p) (op/ns_step_kernel.cu:180-202) and CIP advection of an arbitrary plane set
+ * (op/ns_step_kernel.cu:114-158); strides in elements. */
+int b200_ns_velocity_nonadvect(float* vstar, const float* vel, const float* pres, int B, int H, int W, float dt,
+                               float dx, cudaStream_t stream);
+int b200_ns_cip_advect(float* out, const float* field, const float* vel, long long field_bstride,
+                       long long out_bstride, int B, int H, int W, float dt, float dx, cudaStream_t stream);
+
+/* ---- reverse-SDE state updates --------------------------------------------------------------
+ * replaces the elementwise/reduction torch calls of sampling.py:181-187, 195-200, 213-233, 262-282, 299-319.
+ * x, score, z, x_mean: [B, n_per] fp32.  z == NULL -> Philox4x32-10 noise generated in registers from
+ * (seed, offset, elem_base + element index); elem_base (multiple of 4) is the shard's global element offset.
+ * `step` != NULL -> coefficient index is *step for every sample (per-step tables, CUDA-graph friendly). */
+int b200_sample_sumsq(float* ss_score, float* ss_noise, const float* score, const float* z, int B, long long n_per,
+                      uint64_t seed, uint64_t offset, long long elem_base, cudaStream_t stream);
+int b200_langevin_norm_sums(float* sums2, const float* ss_score, const float* ss_noise, int B, cudaStream_t stream);
+int b200_sde_update(float* x, float* x_mean, const float* score, const float* z, const float* a, const float* b,
+                    const float* c, const int* step, int langevin, const float* norm_sums, float inv_batch_total,
+                    float snr, int B, long long n_per, uint64_t seed, uint64_t offset, long long elem_base,
+                    cudaStream_t stream);
+int b200_fill_normal(float* out, long long total, float scale, uint64_t seed, uint64_t offset, long long elem_base,
+                     cudaStream_t stream);
+int b200_step_advance(int* step, int delta, cudaStream_t stream);
+
+/* ---- score-network building blocks (channels-last activations) -------------------------------
+ * GroupNorm(+SiLU): replaces nn.GroupNorm + act pairs (models/layerspp.py:219-264, models/layers.py:618-642).
+ * Two sources = the skip-connection concat of models/ncsnpp.py:318 without materialising it. */
+int b200_gn_nsplit(int B, int HW);
+int b200_gn_partial(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G, int nsplit,
+                    float* partial, cudaStream_t stream);
+int b200_gn_apply(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G, int nsplit,
+                  const float* partial, const float* gamma, const float* beta, float eps, int act, void* out,
+                  cudaStream_t stream);
+/* layout changes at the API boundary (NCHW fp32 <-> channels-last), incl. `2x-1` (ncsnpp.py:261) and `h/sigma` (:379) */
+int b200_nchw_to_nhwc(const float* x, void* out, int dtype, int B, int C, int H, int W, int Cp, float scale,
+                      float shift, cudaStream_t stream);
+int b200_nhwc_to_nchw(const void* x, float* out, int dtype, int B, int C, int H, int W, int Cs, const float* mul,
+                      cudaStream_t stream);
+/* time embedding: kind 0 Gaussian Fourier (layerspp.py:32-41), 1 sinusoidal (layers.py:500-514) */
+int b200_temb_embed(const float* labels, const int* step, int kind, const float* fourier_w, int nf, const float* sigmas,
+                    int n_sigmas, int scale_by_sigma, float* emb, float* out_mul, int B, cudaStream_t stream);
+/* out[b,n] = act_out(sum_k act_in(x[b,k]) W[n,k] + bias[n])  -- temb MLP and all Dense_0 layers at once */
+int b200_linear_f32(const float* x, const float* W, const float* bias, float* out, int B, int K, int N, int act_in,
+                    int act_out, cudaStream_t stream);
+int b200_add_scale(const void* a, const void* b, void* out, int dtype, long long n, float s, cudaStream_t stream);
+int b200_nearest_up2_nhwc(const void* x, void* out, int dtype, int B, int H, int W, int C, cudaStream_t stream);
+/* implicit-GEMM convolution on CUDA cores (strict fp32 path + odd shapes); epilogue
+ * out = ((conv + bias[n] + temb[b,n]) + res) * out_scale.  replaces nn.Conv2d / NIN (models/layers.py:96-118,537-546) */
+int b200_conv2d_simt(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
+                     const float* temb, int temb_stride, const void* res, float out_scale, void* out, int out_mode,
+                     const float* sample_mul, int dtype, int B, int H, int W, int Ho, int Wo, int Cout, int KH, int KW,
+                     int stride, int pad_t, int pad_l, cudaStream_t stream);
+/* softmax(q k^T scale) v per image on CUDA cores (models/layerspp.py:82-86); ld* = row strides in elements */
+int b200_attention_simt(const void* q, const void* k, const void* v, void* out, int dtype, int B, int L, int C,
+                        int ldq, int ldk, int ldv, int ldo, float scale, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_SDE_H_ */
