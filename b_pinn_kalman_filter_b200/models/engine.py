@@ -1,0 +1,444 @@
+"""ScoreEngine: executes a score network (NCSN++ / DDPM) as a static plan of C-ABI kernel launches.
+
+Replaces `model(x, labels)` = NCSNpp.forward / DDPM.forward (models/ncsnpp.py:232-381, models/ddpm.py:110-181).
+
+Design:
+  * activations are channels-last [B, H, W, C] in `bf16` (tensor-core mode) or `fp32` (strict mode); NCHW fp32 only
+    at the API boundary;
+  * the network is "compiled" once per batch size into a flat list of (entry point, argument tuple) pairs over a
+    reusable workspace -- no allocation, no host sync and no Python tensor math while it runs, so the whole forward
+    (and the whole PC step around it) can be captured into one CUDA graph;
+  * elementwise work is folded into neighbours: bias + time-embedding + residual + 1/sqrt(2) into conv epilogues,
+    skip-connection concat into two-source GroupNorm / conv loaders, `2x-1` into the input layout change and
+    `h / sigma` into the output one.
+"""
+import ctypes
+import math
+
+import torch
+
+from .. import _lib
+from .._lib import c_float, c_int, c_ll, c_vp
+
+_lib.register_signature("b200_gn_nsplit", [c_int, c_int])
+_lib.register_signature("b200_gn_partial", [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp])
+_lib.register_signature("b200_gn_apply", [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp,
+                                          c_float, c_int, c_vp, c_vp])
+_lib.register_signature("b200_nchw_to_nhwc", [c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_float, c_float, c_vp])
+_lib.register_signature("b200_nhwc_to_nchw", [c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp])
+_lib.register_signature("b200_temb_embed", [c_vp, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_vp, c_vp, c_int, c_vp])
+_lib.register_signature("b200_linear_f32", [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp])
+_lib.register_signature("b200_add_scale", [c_vp, c_vp, c_vp, c_int, c_ll, c_float, c_vp])
+_lib.register_signature("b200_nearest_up2_nhwc", [c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp])
+_lib.register_signature("b200_conv2d_simt", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_vp, c_int,
+                                             c_vp, c_int] + [c_int] * 11 + [c_vp])
+_lib.register_signature("b200_attention_simt", [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                                c_int, c_float, c_vp])
+
+DT_F32, DT_BF16 = 0, 1
+_TORCH_DT = {DT_F32: torch.float32, DT_BF16: torch.bfloat16}
+
+
+class Act:
+    """A channels-last activation living in the workspace."""
+    __slots__ = ("t", "B", "H", "W", "C", "Ct")
+
+    def __init__(self, t, B, H, W, C, Ct=None):
+        self.t, self.B, self.H, self.W, self.C = t, B, H, W, C
+        self.Ct = C if Ct is None else Ct   # channels that carry data (3-channel images live in 8-wide tensors)
+
+    @property
+    def ptr(self):
+        return self.t.data_ptr()
+
+    def at(self, byte_offset):
+        """Pointer argument `byte_offset` bytes into this activation (resolved when the plan is finalised)."""
+        return Ptr(self, byte_offset)
+
+
+class Ptr:
+    __slots__ = ("act", "off")
+
+    def __init__(self, act, off):
+        self.act, self.off = act, off
+
+
+class Workspace:
+    """Size-bucketed free list over torch allocations; buffers are reused in program order (single stream)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.free = {}
+        self.all = []
+        self.bytes = 0
+
+    def take(self, numel, dtype):
+        key = (numel, dtype)
+        lst = self.free.get(key)
+        if lst:
+            return lst.pop()
+        t = torch.empty(numel, device=self.device, dtype=dtype)
+        self.all.append(t)
+        self.bytes += t.numel() * t.element_size()
+        return t
+
+    def give(self, t):
+        self.free.setdefault((t.numel(), t.dtype), []).append(t)
+
+
+class Plan:
+    """Flat launch list for one batch size."""
+
+    def __init__(self, B):
+        self.B = B
+        self.ops = []          # (cfunc, args_without_stream, name)
+        self.keep = []         # tensors that must outlive the plan
+        self.x_in = None       # fp32 NCHW input staging   [B, C, H, W]
+        self.labels = None     # fp32 [B]
+        self.out = None        # fp32 NCHW output
+        self.launches = 0
+
+    def run(self, stream_ptr):
+        for fn, args, name in self.ops:
+            rc = fn(*args, stream_ptr)
+            if rc != 0:
+                _lib.check(rc, name)
+
+
+class Builder:
+    """Emits the plan (or, with dry=True, only walks the network to collect the parameter specification)."""
+
+    def __init__(self, engine, B, dry):
+        self.e = engine
+        self.B = B
+        self.dry = dry
+        self.plan = Plan(B)
+        self.ws = engine.workspace if not dry else None
+        self.lib = _lib.lib() if not dry else None
+        self.dt = engine.dt
+        self.tdt = _TORCH_DT[engine.dt]
+        self.specs = []        # (key, shape, init) in reference order
+        self.dense = []        # (key_prefix, out_ch) of every Dense_0, in order
+        self.temb_all = None   # [B, sum(out_ch)] fp32
+        self.temb_stride = 0
+        self.sample_mul = None
+
+    # ---- parameters -------------------------------------------------------------------------------------------
+    def param(self, key, shape, init):
+        self.specs.append((key, tuple(shape), init))
+        return key
+
+    # ---- workspace --------------------------------------------------------------------------------------------
+    def new(self, H, W, C, Ct=None):
+        """A virtual activation; physical memory is assigned by `finalize` from first/last use (liveness)."""
+        return Act(None, self.B, H, W, C, Ct)
+
+    def finalize(self):
+        """Linear-scan buffer assignment over the recorded launches, then bake the argument tuples."""
+        first, last = {}, {}
+        acts = {}
+        for i, (_, args, _) in enumerate(self.plan.ops):
+            for a in args:
+                act = a if isinstance(a, Act) else (a.act if isinstance(a, Ptr) else None)
+                if act is not None:
+                    acts[id(act)] = act
+                    first.setdefault(id(act), i)
+                    last[id(act)] = i
+        born, dies = {}, {}
+        for k, i in first.items():
+            born.setdefault(i, []).append(k)
+        for k, i in last.items():
+            dies.setdefault(i, []).append(k)
+        baked = []
+        for i, (fn, args, name) in enumerate(self.plan.ops):
+            for k in born.get(i, ()):
+                act = acts[k]
+                act.t = self.ws.take(act.B * act.H * act.W * act.C, self.tdt)
+            out = []
+            for a in args:
+                if isinstance(a, Act):
+                    out.append(a.t.data_ptr())
+                elif isinstance(a, Ptr):
+                    out.append(a.act.t.data_ptr() + a.off)
+                else:
+                    out.append(a)
+            baked.append((fn, tuple(out), name))
+            for k in dies.get(i, ()):
+                self.ws.give(acts[k].t)
+        self.plan.ops = baked
+        self.plan.launches = len(baked)
+
+    def f32(self, numel):
+        t = torch.empty(numel, device=self.e.device, dtype=torch.float32)
+        self.plan.keep.append(t)
+        return t
+
+    def emit(self, name, *args):
+        fn = getattr(self.lib, name)
+        self.plan.ops.append((fn, args, name))
+
+    # ---- primitives -------------------------------------------------------------------------------------------
+    def gn(self, x, key, groups, act, x2=None):
+        """GroupNorm(+SiLU) over one or two (concatenated) sources -> new activation."""
+        C = x.C + (x2.C if x2 is not None else 0)
+        self.param(key + ".weight", (C,), "ones")
+        self.param(key + ".bias", (C,), "zeros")
+        out = self.new(x.H, x.W, C)
+        if self.dry:
+            return out
+        HW = x.H * x.W
+        ns = self.lib.b200_gn_nsplit(self.B, HW)
+        part = self.f32(self.B * ns * groups * 2)
+        p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+        self.emit("b200_gn_partial", x, x.C, p2, c2, self.dt, self.B, HW, groups, ns, part.data_ptr())
+        self.emit("b200_gn_apply", x, x.C, p2, c2, self.dt, self.B, HW, groups, ns, part.data_ptr(),
+                  self.e.dev(key + ".weight"), self.e.dev(key + ".bias"), 1e-6, 1 if act else 0, out)
+        return out
+
+    def conv(self, x, key, cout, ksize, x2=None, stride=1, pad=None, out_hw=None, temb_off=None, res=None,
+             out_scale=1.0, init_scale=1.0, nin=False, cout_store=None, nchw_out=None):
+        """Convolution with fused epilogue.  `nin=True`: weight stored as NIN.W [Cin, Cout] (models/layers.py:540).
+        `cout_store` > cout pads the output channels with zeros (3-channel image pyramids live in 8-wide tensors)."""
+        cin = x.C + (x2.C if x2 is not None else 0)
+        cin_true = x.Ct + (x2.Ct if x2 is not None else 0)
+        if nin:
+            self.param(key + ".W", (cin_true, cout), ("default", init_scale))
+            self.param(key + ".b", (cout,), "zeros")
+        else:
+            self.param(key + ".weight", (cout, cin_true, ksize, ksize), ("default", init_scale))
+            self.param(key + ".bias", (cout,), "zeros")
+        if pad is None:
+            pad = (ksize // 2, ksize // 2)
+        Ho, Wo = out_hw if out_hw is not None else (x.H, x.W)
+        cs = cout_store or cout
+        if nchw_out is not None:
+            out = None
+        else:
+            out = self.new(Ho, Wo, cs, cout)
+        if self.dry:
+            return out
+        w = self.e.packed_conv(key, nin, cin, cs)
+        bias = self.e.packed_bias(key, nin, cs)
+        temb_ptr = None
+        if temb_off is not None:
+            temb_ptr = self.temb_all.data_ptr() + 4 * temb_off
+        p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+        if nchw_out is not None:
+            self.emit("b200_conv2d_simt", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, self.temb_stride,
+                      res, out_scale, nchw_out.data_ptr(), 1,
+                      self.sample_mul.data_ptr() if self.sample_mul is not None else None, self.dt, self.B, x.H, x.W,
+                      Ho, Wo, cout, ksize, ksize, stride, pad[0], pad[1])
+            return None
+        self.e.emit_conv(self, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, stride, pad, key)
+        return out
+
+    def upfirdn(self, x, up, down, pad):
+        Ho = (x.H * up + pad[0] + pad[1] - 4) // down + 1
+        Wo = (x.W * up + pad[0] + pad[1] - 4) // down + 1
+        out = self.new(Ho, Wo, x.C, x.Ct)
+        if self.dry:
+            return out
+        k = self.e.fir_kernel(up)
+        self.emit("b200_upfirdn2d_nhwc", x, k.data_ptr(), out, self.dt, self.B, x.H, x.W, x.C, 4, 4, up, down,
+                  pad[0], pad[1])
+        return out
+
+    def nearest_up2(self, x):
+        out = self.new(x.H * 2, x.W * 2, x.C)
+        if not self.dry:
+            self.emit("b200_nearest_up2_nhwc", x, out, self.dt, self.B, x.H, x.W, x.C)
+        return out
+
+    def attention_core(self, qkv, C):
+        """softmax(q k^T / sqrt(C)) v from a fused [B, L, 3C] projection."""
+        out = self.new(qkv.H, qkv.W, C)
+        if self.dry:
+            return out
+        L = qkv.H * qkv.W
+        es = 2 if self.dt == DT_BF16 else 4
+        self.e.emit_attention(self, qkv, out, L, C, es)
+        return out
+
+
+class _SpecOnly:
+    """Stand-in engine for dry walks (parameter specification on machines without a GPU)."""
+
+    def __init__(self, config, dt=DT_BF16):
+        self.config, self.dt, self.workspace = config, dt, None
+
+
+def parameter_spec(config, net_builder):
+    """[(key, shape, init)] of the network in reference order, and the Dense_0 layout; needs no device."""
+    b = Builder(_SpecOnly(config), 1, dry=True)
+    net_builder(b, config)
+    return b.specs, list(b.dense)
+
+
+class ScoreEngine:
+    """Holds packed weights + per-batch-size plans for one network on one device."""
+
+    def __init__(self, config, net_builder, device, precision="bf16", use_tensor_cores=True):
+        if torch.device(device).type != "cuda":
+            raise RuntimeError("ScoreEngine needs a CUDA device; there is no CPU fallback")
+        self.config = config
+        self.net_builder = net_builder
+        self.device = torch.device(device)
+        self.precision = precision
+        self.dt = {"bf16": DT_BF16, "fp32": DT_F32}[precision]
+        self.use_tc = bool(use_tensor_cores) and self.dt == DT_BF16
+        self.workspace = Workspace(self.device)
+        self.params = {}           # reference-layout fp32 tensors on device
+        self._packed = {}
+        self._dev = {}
+        self._fir = {}
+        self.plans = {}
+        self.graphs = {}
+        self.version = 0
+        self._spec = None
+        self.dense_layout = []
+        self.dense_total = 0
+        self.tc_convs = 0
+        self.simt_convs = 0
+
+    # ---- parameters -------------------------------------------------------------------------------------------
+    def spec(self):
+        """Parameter specification [(key, shape, init)] + layout of the batched Dense_0 projection."""
+        if self._spec is None:
+            self._spec, self.dense_layout = parameter_spec(self.config, self.net_builder)
+            self.dense_total = sum(c for _, c in self.dense_layout)
+        return self._spec
+
+    def packed_dense(self):
+        """All Dense_0 layers stacked: W [sum(out_ch), 4nf], b [sum(out_ch)] (fp32)."""
+        if "dense" not in self._packed:
+            w = torch.cat([self.params[k + ".weight"] for k, _ in self.dense_layout], 0).contiguous()
+            bb = torch.cat([self.params[k + ".bias"] for k, _ in self.dense_layout], 0).contiguous()
+            self._packed["dense"] = (w, bb)
+        return self._packed["dense"]
+
+    def packed_qkv(self, p, C):
+        """NIN_0/1/2 stacked into one [3C][1][1][C] weight (+ [3C] bias): q, k, v in one GEMM."""
+        pk = (p, "qkv")
+        if pk not in self._packed:
+            w = torch.cat([self.params[p + ".NIN_%d.W" % i].t() for i in range(3)], 0)   # [3C, C]
+            bb = torch.cat([self.params[p + ".NIN_%d.b" % i] for i in range(3)], 0)
+            self._packed[pk] = (w.reshape(3 * C, 1, 1, C).to(_TORCH_DT[self.dt]).contiguous(), bb.contiguous())
+        return self._packed[pk]
+
+    def load_state_dict(self, sd, strict=True):
+        spec = self.spec()
+        new = {}
+        for key, shape, _ in spec:
+            src = None
+            for cand in (key, "module." + key):
+                if cand in sd:
+                    src = sd[cand]
+                    break
+            if src is None:
+                if strict:
+                    raise KeyError("missing parameter %s" % key)
+                continue
+            if tuple(src.shape) != tuple(shape):
+                raise RuntimeError("shape mismatch for %s: %s vs %s" % (key, tuple(src.shape), shape))
+            new[key] = src.detach().to(device=self.device, dtype=torch.float32).contiguous()
+        self.params.update(new)
+        self._packed.clear()
+        self._dev.clear()
+        self.plans.clear()
+        self.graphs.clear()
+        self.workspace = Workspace(self.device)
+        self.version += 1
+
+    def state_dict(self):
+        return dict(self.params)
+
+    def dev(self, key):
+        return self.params[key].data_ptr()
+
+    def fir_kernel(self, up):
+        """outer([1,3,3,1]) normalised, times up^2 (models/up_or_down_sampling.py:181-188, 221, 254)."""
+        if up not in self._fir:
+            k1 = torch.tensor(self.config.model.fir_kernel, dtype=torch.float32)
+            k = torch.outer(k1, k1)
+            k = k / k.sum() * (up ** 2)
+            self._fir[up] = k.to(self.device).contiguous()
+        return self._fir[up]
+
+    def packed_conv(self, key, nin, cin_store, cout_store):
+        """[Cout_store][KH][KW][Cin_store] in the activation dtype, zero padded."""
+        pk = (key, cin_store, cout_store)
+        if pk not in self._packed:
+            if nin:
+                w = self.params[key + ".W"].t().contiguous()[:, :, None, None]   # [Cout, Cin, 1, 1]
+            else:
+                w = self.params[key + ".weight"]
+            cout, cin, kh, kw = w.shape
+            p = torch.zeros(cout_store, kh, kw, cin_store, device=self.device, dtype=torch.float32)
+            p[:cout, :, :, :cin] = w.permute(0, 2, 3, 1)
+            self._packed[pk] = p.to(_TORCH_DT[self.dt]).contiguous()
+        return self._packed[pk]
+
+    def packed_bias(self, key, nin, cout_store):
+        pk = (key, "bias", cout_store)
+        if pk not in self._packed:
+            b = self.params[key + (".b" if nin else ".bias")]
+            p = torch.zeros(cout_store, device=self.device, dtype=torch.float32)
+            p[:b.numel()] = b
+            self._packed[pk] = p
+        return self._packed[pk]
+
+    # ---- kernel selection -------------------------------------------------------------------------------------
+    def emit_conv(self, b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, stride, pad, key):
+        from . import tc
+        if self.use_tc and tc.conv_supported(x, x2, out, ksize, stride, pad):
+            tc.emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, pad)
+            self.tc_convs += 1
+            return
+        self.simt_convs += 1
+        p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+        b.emit("b200_conv2d_simt", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, b.temb_stride,
+               res, out_scale, out, 0, None, self.dt, b.B, x.H, x.W, out.H, out.W,
+               out.C, ksize, ksize, stride, pad[0], pad[1])
+
+    def emit_attention(self, b, qkv, out, L, C, es):
+        from . import tc
+        if self.use_tc and tc.attention_supported(L, C):
+            tc.emit_attention(b, qkv, out, L, C)
+            return
+        b.emit("b200_attention_simt", qkv, qkv.at(C * es), qkv.at(2 * C * es), out, self.dt, b.B, L, C, 3 * C, 3 * C,
+               3 * C, C, float(int(C) ** (-0.5)))
+
+    # ---- plans ------------------------------------------------------------------------------------------------
+    def plan(self, B):
+        if B not in self.plans:
+            if not self.params:
+                raise RuntimeError("ScoreEngine has no weights; call load_state_dict / init_weights first")
+            with torch.cuda.device(self.device):
+                self.spec()
+                b = Builder(self, B, dry=False)
+                self.net_builder(b, self.config)
+                b.finalize()
+                self.plans[B] = b.plan
+        return self.plans[B]
+
+    def forward(self, x, labels, out=None):
+        """x: [B, C, H, W] fp32 CUDA; labels: [B] (sigma for Fourier nets, timestep index/continuous otherwise)."""
+        _lib.require_cuda(x, labels)
+        B = x.shape[0]
+        p = self.plan(B)
+        with torch.cuda.device(self.device):
+            p.x_in.copy_(x)
+            p.labels.copy_(labels.to(torch.float32).reshape(B))
+            p.run(_lib.stream())
+            if out is None:
+                return p.out.clone()
+            out.copy_(p.out)
+            return out
+
+    def run_inplace(self, B):
+        """Runs the plan on whatever is already in plan.x_in / plan.labels (used by the fused sampler)."""
+        p = self.plans[B]
+        p.run(_lib.stream())
+        return p.out
+
+    __call__ = forward

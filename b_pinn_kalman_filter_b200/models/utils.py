@@ -1,0 +1,193 @@
+"""Model registry, model creation and score functions with the reference's API (models/utils.py:24-187).
+
+`create_model(config)` returns a `ScoreModel`: a callable `model(x, labels)` that runs the network on the B200
+score engine.  It mimics what the sampling code touches on the reference's `nn.DataParallel(model)`:
+`.eval()`, `.train()`, `.module`, `state_dict()`, `load_state_dict()`, `parameters()`.
+"""
+import math
+
+import numpy as np
+import torch
+
+from .. import sde_lib
+from .engine import ScoreEngine
+
+_MODELS = {}
+
+
+def register_model(cls=None, *, name=None):
+    """A decorator for registering model builders (same contract as models/utils.py:27-43)."""
+
+    def _register(cls):
+        local_name = cls.__name__ if name is None else name
+        if local_name in _MODELS:
+            raise ValueError(f'Already registered model with name: {local_name}')
+        _MODELS[local_name] = cls
+        return cls
+
+    if cls is None:
+        return _register
+    return _register(cls)
+
+
+def get_model(name):
+    return _MODELS[name]
+
+
+def get_sigmas(config):
+    """models/utils.py:50-60"""
+    return np.exp(np.linspace(np.log(config.model.sigma_max), np.log(config.model.sigma_min), config.model.num_scales))
+
+
+def get_ddpm_params(config):
+    """models/utils.py:63-85"""
+    num_diffusion_timesteps = 1000
+    beta_start = config.model.beta_min / config.model.num_scales
+    beta_end = config.model.beta_max / config.model.num_scales
+    betas = np.linspace(beta_start, beta_end, num_diffusion_timesteps, dtype=np.float64)
+    alphas = 1. - betas
+    alphas_cumprod = np.cumprod(alphas, axis=0)
+    return {
+        'betas': betas, 'alphas': alphas, 'alphas_cumprod': alphas_cumprod,
+        'sqrt_alphas_cumprod': np.sqrt(alphas_cumprod), 'sqrt_1m_alphas_cumprod': np.sqrt(1. - alphas_cumprod),
+        'beta_min': beta_start * (num_diffusion_timesteps - 1), 'beta_max': beta_end * (num_diffusion_timesteps - 1),
+        'num_diffusion_timesteps': num_diffusion_timesteps}
+
+
+def _fans(shape):
+    rf = float(np.prod(shape)) / shape[1] / shape[0]
+    return shape[1] * rf, shape[0] * rf
+
+
+def init_tensor(shape, init, gen):
+    """Random initialisation with the reference's distributions (models/layers.py:53-86 `default_init` =
+    variance_scaling(scale, 'fan_avg', 'uniform') with in_axis=1, out_axis=0; scale 0 -> 1e-10)."""
+    if init == "zeros":
+        return torch.zeros(shape)
+    if init == "ones":
+        return torch.ones(shape)
+    kind, scale = init
+    if kind == "randn":
+        return torch.randn(shape, generator=gen) * scale
+    scale = 1e-10 if scale == 0 else scale
+    if len(shape) == 1:
+        fan_in = fan_out = shape[0]
+    else:
+        fan_in, fan_out = _fans(shape)
+    variance = scale / ((fan_in + fan_out) / 2)
+    return (torch.rand(shape, generator=gen) * 2. - 1.) * math.sqrt(3 * variance)
+
+
+class ScoreModel:
+    """The object `create_model` returns; stands where the reference has nn.DataParallel(NCSNpp(config))."""
+
+    def __init__(self, config, device=None, precision=None, seed=None, init=True):
+        name = config.model.name
+        device = torch.device(device if device is not None else config.device)
+        precision = precision or getattr(config.model, "b200_precision", "bf16")
+        self.config = config
+        self.engine = ScoreEngine(config, get_model(name), device, precision=precision)
+        self.training = False
+        self.module = self          # `.module` of DataParallel
+        if init:
+            self.init_weights(config.seed if seed is None else seed)
+
+    # -- parameters --
+    def init_weights(self, seed):
+        gen = torch.Generator().manual_seed(int(seed))
+        sd = {key: init_tensor(shape, init, gen) for key, shape, init in self.engine.spec()}
+        sd["sigmas"] = torch.tensor(get_sigmas(self.config), dtype=torch.float32)
+        self.engine.params["sigmas"] = sd["sigmas"].to(self.engine.device)
+        self.engine.load_state_dict(sd)
+
+    def state_dict(self):
+        return {k: v.clone() for k, v in self.engine.state_dict().items()}
+
+    def load_state_dict(self, sd, strict=True):
+        """Accepts the reference's checkpoints: keys `[module.]all_modules.<i>.<name>` and `[module.]sigmas`."""
+        for k in ("sigmas", "module.sigmas"):
+            if k in sd:
+                self.engine.params["sigmas"] = sd[k].detach().to(self.engine.device, torch.float32).contiguous()
+        self.engine.load_state_dict(sd, strict=strict)
+
+    def parameters(self):
+        return [v for k, v in self.engine.params.items() if k != "sigmas"]
+
+    def to(self, *a, **k):
+        return self
+
+    def eval(self):
+        self.training = False
+        return self
+
+    def train(self, mode=True):
+        if mode:
+            raise NotImplementedError("the B200 engine implements the sampling (eval) path only")
+        self.training = False
+        return self
+
+    def __call__(self, x, labels):
+        return self.engine.forward(x, labels)
+
+    forward = __call__
+
+
+def create_model(config, precision=None, seed=None):
+    """models/utils.py:88-94"""
+    import b_pinn_kalman_filter_b200.models  # noqa: F401  (registers the builders)
+    return ScoreModel(config, precision=precision, seed=seed)
+
+
+def get_model_fn(model, train=False):
+    """models/utils.py:97-126"""
+
+    def model_fn(x, labels):
+        if not train:
+            model.eval()
+            return model(x, labels)
+        model.train()
+        return model(x, labels)
+
+    return model_fn
+
+
+def get_score_fn(sde, model, train=False, continuous=False):
+    """models/utils.py:129-178: label construction + sign/scale of the network output."""
+    model_fn = get_model_fn(model, train=train)
+
+    if isinstance(sde, sde_lib.VPSDE) or isinstance(sde, sde_lib.subVPSDE):
+        def score_fn(x, t):
+            if continuous or isinstance(sde, sde_lib.subVPSDE):
+                labels = t * 999
+                score = model_fn(x, labels)
+                std = sde.marginal_prob(torch.zeros_like(x), t)[1]
+            else:
+                labels = t * (sde.N - 1)
+                score = model_fn(x, labels)
+                std = sde.sqrt_1m_alphas_cumprod.to(labels.device)[labels.long()]
+            score = -score / std[:, None, None, None]
+            return score
+
+    elif isinstance(sde, sde_lib.VESDE):
+        def score_fn(x, t):
+            if continuous:
+                labels = sde.marginal_prob(torch.zeros_like(x), t)[1]
+            else:
+                labels = sde.T - t
+                labels *= sde.N - 1
+                labels = torch.round(labels).long()
+            score = model_fn(x, labels)
+            return score
+
+    else:
+        raise NotImplementedError(f"SDE class {sde.__class__.__name__} not yet supported.")
+
+    return score_fn
+
+
+def to_flattened_numpy(x):
+    return x.detach().cpu().numpy().reshape((-1,))
+
+
+def from_flattened_numpy(x, shape):
+    return torch.from_numpy(x.reshape(shape))

@@ -1,0 +1,613 @@
+"""Predictor-corrector sampling with the reference's plugin API (sampling.py:30-411) on the B200 kernels.
+
+Public surface kept verbatim: `register_predictor/corrector`, `get_predictor/corrector`, `get_sampling_fn`,
+`get_pc_sampler`, `shared_predictor_update_fn`, `shared_corrector_update_fn`, classes `Predictor`, `Corrector`,
+the predictors `euler_maruyama`, `reverse_diffusion`, `ancestral_sampling`, `none` and the correctors `langevin`,
+`ald`, `none`.
+
+How it runs:
+  * every built-in update is `x_mean = a x + b s ; x = x_mean + c z` with per-sample scalars, executed by ONE fused
+    kernel (csrc/sde_update.cu) that also generates z (Philox) unless a noise source is injected;
+  * `get_pc_sampler(...)(model)` with a B200 `ScoreModel` and built-in predictor/corrector classes takes the fused
+    loop: per-step scalar tables live on the device, the score network reads its label from the table at a device
+    step counter, so a whole PC step is a fixed launch sequence (CUDA-graph replayed N times, no host sync);
+  * user-registered Predictor/Corrector subclasses still work: the loop then calls their `update_fn` around the engine.
+"""
+import abc
+import functools
+import math
+
+import numpy as np
+import torch
+
+from . import _lib, sde_lib
+from .models import utils as mutils
+from .models.utils import get_score_fn
+
+_CORRECTORS = {}
+_PREDICTORS = {}
+
+# Optional noise source for parity tests: callable(shape, device) -> fp32 tensor; None = fused Philox on device.
+NOISE_FN = None
+# Philox stream id source for the fused generator.
+_SEED = [0x5DEECE66D]
+
+
+def set_seed(seed):
+    _SEED[0] = int(seed) & 0xFFFFFFFFFFFFFFFF
+
+
+def _register(table, kind):
+    def deco(cls=None, *, name=None):
+        def _do(cls):
+            local_name = cls.__name__ if name is None else name
+            if local_name in table:
+                raise ValueError(f'Already registered model with name: {local_name}')
+            table[local_name] = cls
+            return cls
+        return _do if cls is None else _do(cls)
+    deco.__doc__ = "A decorator for registering %s classes." % kind
+    return deco
+
+
+register_predictor = _register(_PREDICTORS, "predictor")
+register_corrector = _register(_CORRECTORS, "corrector")
+
+
+def get_predictor(name):
+    return _PREDICTORS[name]
+
+
+def get_corrector(name):
+    return _CORRECTORS[name]
+
+
+def get_sampling_fn(config, sde, shape, inverse_scaler, eps):
+    """sampling.py:80-123"""
+    sampler_name = config.sampling.method
+    if sampler_name.lower() == 'ode':
+        return get_ode_sampler(sde=sde, shape=shape, inverse_scaler=inverse_scaler,
+                               denoise=config.sampling.noise_removal, eps=eps, device=config.device)
+    if sampler_name.lower() == 'pc':
+        return get_pc_sampler(sde=sde, shape=shape,
+                              predictor=get_predictor(config.sampling.predictor.lower()),
+                              corrector=get_corrector(config.sampling.corrector.lower()),
+                              inverse_scaler=inverse_scaler, snr=config.sampling.snr,
+                              n_steps=config.sampling.n_steps_each,
+                              probability_flow=config.sampling.probability_flow,
+                              continuous=config.training.continuous, denoise=config.sampling.noise_removal,
+                              eps=eps, device=config.device)
+    raise ValueError(f"Sampler name {sampler_name} unknown.")
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# fused elementwise update (the only place [B,C,H,W]-sized sampler arithmetic happens)
+# ------------------------------------------------------------------------------------------------------------------
+def _noise(shape, device):
+    return None if NOISE_FN is None else NOISE_FN(tuple(shape), device).to(device=device, dtype=torch.float32).contiguous()
+
+
+def fused_update(x, score, a, b, c, z=None, seed=None, offset=0, elem_base=0):
+    """Returns (x_new, x_mean) with x_mean = a x + b score, x_new = x_mean + c z; a/b/c are [B] tensors (a, c may be
+    None = 1, 0).  z None -> Philox noise generated inside the kernel."""
+    _lib.require_cuda(x, score)
+    B = x.shape[0]
+    n_per = x[0].numel()
+    xn = x.detach().to(torch.float32).contiguous().clone()
+    xm = torch.empty_like(xn)
+    s = score.detach().to(torch.float32).contiguous()
+    f = lambda v: None if v is None else v.detach().to(device=x.device, dtype=torch.float32).contiguous()
+    a, b, c, z = f(a), f(b), f(c), f(z)
+    with torch.cuda.device(x.device):
+        rc = _lib.lib().b200_sde_update(_lib.ptr(xn), _lib.ptr(xm), _lib.ptr(s), _lib.ptr(z), _lib.ptr(a), _lib.ptr(b),
+                                        _lib.ptr(c), None, 0, None, 0.0, 0.0, B, n_per,
+                                        _SEED[0] if seed is None else seed, offset, elem_base, _lib.stream())
+    _lib.check(rc, "b200_sde_update")
+    return xn, xm
+
+
+_OFFSET = [0]
+
+
+def _next_offset():
+    _OFFSET[0] += 1
+    return _OFFSET[0]
+
+
+def _index(sde, t):
+    return (t * (sde.N - 1) / sde.T).long()
+
+
+class Predictor(abc.ABC):
+    """The abstract class for a predictor algorithm."""
+
+    def __init__(self, sde, score_fn, probability_flow=False):
+        super().__init__()
+        self.sde = sde
+        self.rsde = sde.reverse(score_fn, probability_flow)
+        self.score_fn = score_fn
+
+    @abc.abstractmethod
+    def update_fn(self, x, t):
+        """One predictor update: returns (x, x_mean)."""
+
+
+class Corrector(abc.ABC):
+    """The abstract class for a corrector algorithm."""
+
+    def __init__(self, sde, score_fn, snr, n_steps):
+        super().__init__()
+        self.sde = sde
+        self.score_fn = score_fn
+        self.snr = snr
+        self.n_steps = n_steps
+
+    @abc.abstractmethod
+    def update_fn(self, x, t):
+        """One corrector update: returns (x, x_mean)."""
+
+
+def _apply(x, score, a, b, c):
+    z = _noise(x.shape, x.device)
+    return fused_update(x, score, a, b, c, z=z, offset=_next_offset())
+
+
+@register_predictor(name='euler_maruyama')
+class EulerMaruyamaPredictor(Predictor):
+    """x_mean = x + (f(x,t) - g^2 s [/2]) dt, x = x_mean + g sqrt(-dt) z, dt = -1/N   (sampling.py:181-187)."""
+
+    def coefficients(self, t):
+        drift_coef, g = self.sde.coefficient(t)        # linear SDEs: f = drift_coef * x
+        dt = -1. / self.rsde.N
+        w = 0.5 if self.rsde.probability_flow else 1.
+        a = 1. + drift_coef * dt
+        b = -(g ** 2) * w * dt
+        c = torch.zeros_like(g) if self.rsde.probability_flow else g * math.sqrt(-dt)
+        return a, b, c
+
+    def update_fn(self, x, t):
+        a, b, c = self.coefficients(t)
+        return _apply(x, self.score_fn(x, t), a, b, c)
+
+
+@register_predictor(name='reverse_diffusion')
+class ReverseDiffusionPredictor(Predictor):
+    """x_mean = x - f + G^2 s [/2], x = x_mean + G z   (sampling.py:195-200 + RSDE.discretize sde_lib.py:112-117)."""
+
+    def coefficients(self, t):
+        sde = self.sde
+        w = 0.5 if self.rsde.probability_flow else 1.
+        if isinstance(sde, sde_lib.VESDE):
+            i = _index(sde, t)
+            table = sde.discrete_sigmas.to(t.device)
+            sigma = table[i]
+            adjacent = torch.where(i == 0, torch.zeros_like(t), table[i - 1])
+            G = torch.sqrt(sigma ** 2 - adjacent ** 2)
+            a = torch.ones_like(G)
+        elif isinstance(sde, sde_lib.VPSDE):
+            i = _index(sde, t)
+            beta = sde.discrete_betas.to(t.device)[i]
+            G = torch.sqrt(beta)
+            a = 2. - torch.sqrt(sde.alphas.to(t.device)[i])     # x - (sqrt(alpha) x - x)
+        else:                                                     # Euler-Maruyama discretisation (sde_lib.py:62-79)
+            drift_coef, g = sde.coefficient(t)
+            a = 1. - drift_coef / sde.N
+            G = g * math.sqrt(1. / sde.N)
+        b = G ** 2 * w
+        c = torch.zeros_like(G) if self.rsde.probability_flow else G
+        return a, b, c
+
+    def update_fn(self, x, t):
+        a, b, c = self.coefficients(t)
+        return _apply(x, self.score_fn(x, t), a, b, c)
+
+
+@register_predictor(name='ancestral_sampling')
+class AncestralSamplingPredictor(Predictor):
+    """The ancestral sampling predictor (VE / VP only; sampling.py:203-239)."""
+
+    def __init__(self, sde, score_fn, probability_flow=False):
+        super().__init__(sde, score_fn, probability_flow)
+        if not isinstance(sde, sde_lib.VPSDE) and not isinstance(sde, sde_lib.VESDE):
+            raise NotImplementedError(f"SDE class {sde.__class__.__name__} not yet supported.")
+        assert not probability_flow, "Probability flow not supported by ancestral sampling"
+
+    def coefficients(self, t):
+        sde = self.sde
+        i = _index(sde, t)
+        if isinstance(sde, sde_lib.VESDE):
+            table = sde.discrete_sigmas.to(t.device)
+            sigma = table[i]
+            adjacent = torch.where(i == 0, torch.zeros_like(t), table[i - 1])
+            b = sigma ** 2 - adjacent ** 2
+            c = torch.sqrt((adjacent ** 2 * (sigma ** 2 - adjacent ** 2)) / (sigma ** 2))
+            return torch.ones_like(b), b, c
+        beta = sde.discrete_betas.to(t.device)[i]
+        inv = 1. / torch.sqrt(1. - beta)
+        return inv, beta * inv, torch.sqrt(beta)
+
+    def update_fn(self, x, t):
+        a, b, c = self.coefficients(t)
+        return _apply(x, self.score_fn(x, t), a, b, c)
+
+
+@register_predictor(name='none')
+class NonePredictor(Predictor):
+    """An empty predictor that does nothing."""
+
+    def __init__(self, sde, score_fn, probability_flow=False):
+        pass
+
+    def update_fn(self, x, t):
+        return x, x
+
+
+def _alpha(sde, t):
+    if isinstance(sde, sde_lib.VPSDE) or isinstance(sde, sde_lib.subVPSDE):
+        return sde.alphas.to(t.device)[_index(sde, t)]
+    return torch.ones_like(t)
+
+
+def _check_corrector_sde(sde):
+    if not isinstance(sde, (sde_lib.VPSDE, sde_lib.VESDE, sde_lib.subVPSDE)):
+        raise NotImplementedError(f"SDE class {sde.__class__.__name__} not yet supported.")
+
+
+@register_corrector(name='langevin')
+class LangevinCorrector(Corrector):
+    """step = 2 alpha (snr |z| / |s|)^2 with batch-mean norms; x_mean = x + step s; x = x_mean + sqrt(2 step) z
+    (sampling.py:262-282)."""
+
+    def __init__(self, sde, score_fn, snr, n_steps):
+        super().__init__(sde, score_fn, snr, n_steps)
+        _check_corrector_sde(sde)
+
+    def update_fn(self, x, t):
+        alpha = _alpha(self.sde, t)
+        x_mean = x
+        for _ in range(self.n_steps):
+            grad = self.score_fn(x, t)
+            x, x_mean = langevin_update(x, grad, alpha, self.snr)
+        return x, x_mean
+
+
+def langevin_update(x, grad, alpha, snr, z=None, process_group=None):
+    """One fused Langevin step (norm pass + update pass).  With a process group the two batch-mean norms are
+    all-reduced so that sharded batches reproduce the single-device step size exactly."""
+    _lib.require_cuda(x, grad)
+    lib = _lib.lib()
+    B = x.shape[0]
+    n_per = x[0].numel()
+    dev = x.device
+    if z is None:
+        z = _noise(x.shape, dev)
+    xn = x.detach().to(torch.float32).contiguous().clone()
+    xm = torch.empty_like(xn)
+    g = grad.detach().to(torch.float32).contiguous()
+    al = alpha.detach().to(device=dev, dtype=torch.float32).contiguous()
+    ss = torch.empty(2, B, device=dev, dtype=torch.float32)
+    sums = torch.empty(2, device=dev, dtype=torch.float32)
+    seed, off = _SEED[0], _next_offset()
+    total = B
+    with torch.cuda.device(dev):
+        st = _lib.stream()
+        _lib.check(lib.b200_sample_sumsq(_lib.ptr(ss[0]), _lib.ptr(ss[1]), _lib.ptr(g), _lib.ptr(z), B, n_per, seed, off,
+                                         0, st), "b200_sample_sumsq")
+        _lib.check(lib.b200_langevin_norm_sums(_lib.ptr(sums), _lib.ptr(ss[0]), _lib.ptr(ss[1]), B, st),
+                   "b200_langevin_norm_sums")
+        if process_group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(sums, group=process_group)
+            total = B * dist.get_world_size(process_group)
+        _lib.check(lib.b200_sde_update(_lib.ptr(xn), _lib.ptr(xm), _lib.ptr(g), _lib.ptr(z), _lib.ptr(al), None, None,
+                                       None, 1, _lib.ptr(sums), 1.0 / total, float(snr), B, n_per, seed, off, 0, st),
+                   "b200_sde_update")
+    return xn, xm
+
+
+@register_corrector(name='ald')
+class AnnealedLangevinDynamics(Corrector):
+    """step = 2 alpha (snr std(t))^2, no reductions (sampling.py:299-319)."""
+
+    def __init__(self, sde, score_fn, snr, n_steps):
+        super().__init__(sde, score_fn, snr, n_steps)
+        _check_corrector_sde(sde)
+
+    def coefficients(self, t):
+        std = self.sde.marginal_coef(t)[1]
+        step = (self.snr * std) ** 2 * 2 * _alpha(self.sde, t)
+        return torch.ones_like(step), step, torch.sqrt(step * 2)
+
+    def update_fn(self, x, t):
+        a, b, c = self.coefficients(t)
+        x_mean = x
+        for _ in range(self.n_steps):
+            x, x_mean = _apply(x, self.score_fn(x, t), a, b, c)
+        return x, x_mean
+
+
+@register_corrector(name='none')
+class NoneCorrector(Corrector):
+    """An empty corrector that does nothing."""
+
+    def __init__(self, sde, score_fn, snr, n_steps):
+        pass
+
+    def update_fn(self, x, t):
+        return x, x
+
+
+def shared_predictor_update_fn(x, t, sde, model, predictor, probability_flow, continuous):
+    """sampling.py:333-341"""
+    score_fn = mutils.get_score_fn(sde, model, train=False, continuous=continuous)
+    cls = NonePredictor if predictor is None else predictor
+    return cls(sde, score_fn, probability_flow).update_fn(x, t)
+
+
+def shared_corrector_update_fn(x, t, sde, model, corrector, continuous, snr, n_steps):
+    """sampling.py:344-352"""
+    score_fn = mutils.get_score_fn(sde, model, train=False, continuous=continuous)
+    cls = NoneCorrector if corrector is None else corrector
+    return cls(sde, score_fn, snr, n_steps).update_fn(x, t)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# PC sampler
+# ------------------------------------------------------------------------------------------------------------------
+_BUILTIN_PREDICTORS = (EulerMaruyamaPredictor, ReverseDiffusionPredictor, AncestralSamplingPredictor, NonePredictor)
+_BUILTIN_CORRECTORS = (LangevinCorrector, AnnealedLangevinDynamics, NoneCorrector)
+
+
+def _label_and_scale_tables(sde, timesteps, continuous):
+    """Per-step network label and score multiplier (score = mult * model_out): models/utils.py:144-173."""
+    t = timesteps
+    if isinstance(sde, (sde_lib.VPSDE, sde_lib.subVPSDE)):
+        if continuous or isinstance(sde, sde_lib.subVPSDE):
+            labels = t * 999
+            std = sde.marginal_coef(t)[1]
+        else:
+            labels = t * (sde.N - 1)
+            std = sde.sqrt_1m_alphas_cumprod.to(t.device)[labels.long()]
+        return labels, -1.0 / std
+    if isinstance(sde, sde_lib.VESDE):
+        if continuous:
+            labels = sde.marginal_coef(t)[1]
+        else:
+            labels = torch.round((sde.T - t) * (sde.N - 1)).long().to(torch.float32)
+        return labels, torch.ones_like(t)
+    raise NotImplementedError(f"SDE class {sde.__class__.__name__} not yet supported.")
+
+
+class FusedPCLoop:
+    """State + launch sequence of the fused PC loop for one (model, batch) pair.  One `step()` = corrector
+    (n_steps Langevin/ALD updates) + predictor, i.e. (n_steps + 1) score-network forwards."""
+
+    def __init__(self, model, sde, shape, predictor, corrector, snr, n_steps, probability_flow, continuous, eps,
+                 process_group=None, rank_offset=0, total_batch=None, use_graph=True, seed=None):
+        eng = model.engine
+        self.eng = eng
+        self.sde = sde
+        self.shape = tuple(shape)
+        self.B = shape[0]
+        self.n_per = int(np.prod(shape[1:]))
+        self.dev = eng.device
+        self.lib = _lib.lib()
+        self.pg = process_group
+        self.total_batch = total_batch or self.B
+        self.elem_base = rank_offset * self.n_per
+        self.seed = _SEED[0] if seed is None else seed
+        self.snr = float(snr)
+        self.use_graph = use_graph and NOISE_FN is None and process_group is None
+        N = sde.N
+        dev = self.dev
+        t = torch.linspace(sde.T, eps, N, device=dev)
+        labels, mult = _label_and_scale_tables(sde, t, continuous)
+        score_stub = None
+        # predictor tables
+        self.pred = None
+        if predictor is not None and predictor is not NonePredictor:
+            pobj = predictor.__new__(predictor)
+            pobj.sde = sde
+            pobj.rsde = type("R", (), {"N": N, "probability_flow": probability_flow})()
+            a, b, c = pobj.coefficients(t)
+            self.pred = [v.to(torch.float32).contiguous() for v in (a.expand_as(t) if a.dim() else a.repeat(N),
+                                                                   b * mult, c)]
+        # corrector tables
+        self.corr = None
+        self.n_steps = n_steps
+        if corrector is not None and corrector is not NoneCorrector and n_steps > 0:
+            alpha = _alpha(sde, t).to(torch.float32)
+            if corrector is LangevinCorrector:
+                self.corr = ("langevin", alpha.contiguous())
+                self.mult = mult.to(torch.float32).contiguous()
+            else:
+                std = sde.marginal_coef(t)[1]
+                step = (snr * std) ** 2 * 2 * alpha
+                self.corr = ("ald", torch.ones_like(step).contiguous(), (step * mult).to(torch.float32).contiguous(),
+                             torch.sqrt(step * 2).to(torch.float32).contiguous())
+        self.labels = labels.to(torch.float32).contiguous()
+        self.step_dev = torch.zeros(1, device=dev, dtype=torch.int32)
+        self.plan = eng.plan(self.B)
+        # network launches with the label read from the table at *step
+        ops = list(self.plan.ops)
+        fn, args, name = ops[self.plan.temb_op_index]
+        args = (self.labels.data_ptr(), self.step_dev.data_ptr()) + tuple(args[2:])
+        ops[self.plan.temb_op_index] = (fn, args, name)
+        self.net_ops = ops
+        self.x = self.plan.x_in            # the state IS the network's input buffer
+        self.score = self.plan.out
+        self.x_mean = torch.zeros_like(self.x)
+        self.ss = torch.zeros(2, self.B, device=dev, dtype=torch.float32)
+        self.sums = torch.zeros(2, device=dev, dtype=torch.float32)
+        self.scaled = torch.zeros_like(self.x) if (self.corr and self.corr[0] == "langevin" and
+                                                   not bool((mult == 1).all())) else None
+        self.graph = None
+        self.offset = 0
+        self.launches_per_step = 0
+        self.forwards_per_step = (n_steps if self.corr else 0) + (1 if self.pred else 0)
+
+    # -- pieces --
+    def _forward(self, st):
+        for fn, args, name in self.net_ops:
+            rc = fn(*args, st)
+            if rc:
+                _lib.check(rc, name)
+        return len(self.net_ops)
+
+    def _corrector(self, st, off):
+        lib, B, n_per = self.lib, self.B, self.n_per
+        n = self._forward(st)
+        z = _noise(self.shape, self.dev)
+        zp = _lib.ptr(z)
+        if self.corr[0] == "langevin":
+            score = self.score
+            if self.scaled is not None:
+                # VP: grad = -model/std; Langevin needs |grad| -> materialise the scaled score once (rare path)
+                torch.mul(self.score, self.mult[self.step_host].item(), out=self.scaled)
+                score = self.scaled
+            _lib.check(lib.b200_sample_sumsq(_lib.ptr(self.ss[0]), _lib.ptr(self.ss[1]), _lib.ptr(score), zp, B, n_per,
+                                             self.seed, off, self.elem_base, st), "b200_sample_sumsq")
+            _lib.check(lib.b200_langevin_norm_sums(_lib.ptr(self.sums), _lib.ptr(self.ss[0]), _lib.ptr(self.ss[1]), B,
+                                                   st), "b200_langevin_norm_sums")
+            if self.pg is not None:
+                import torch.distributed as dist
+                dist.all_reduce(self.sums, group=self.pg)
+            _lib.check(lib.b200_sde_update(_lib.ptr(self.x), _lib.ptr(self.x_mean), _lib.ptr(score), zp,
+                                           _lib.ptr(self.corr[1]), None, None, _lib.ptr(self.step_dev), 1,
+                                           _lib.ptr(self.sums), 1.0 / self.total_batch, self.snr, B, n_per, self.seed,
+                                           off, self.elem_base, st), "b200_sde_update")
+            return n + 3
+        _, a, b, c = self.corr
+        _lib.check(lib.b200_sde_update(_lib.ptr(self.x), _lib.ptr(self.x_mean), _lib.ptr(self.score), zp, _lib.ptr(a),
+                                       _lib.ptr(b), _lib.ptr(c), _lib.ptr(self.step_dev), 0, None, 0.0, 0.0, B, n_per,
+                                       self.seed, off, self.elem_base, st), "b200_sde_update")
+        return n + 1
+
+    def _predictor(self, st, off):
+        n = self._forward(st)
+        z = _noise(self.shape, self.dev)
+        a, b, c = self.pred
+        _lib.check(self.lib.b200_sde_update(_lib.ptr(self.x), _lib.ptr(self.x_mean), _lib.ptr(self.score), _lib.ptr(z),
+                                            _lib.ptr(a), _lib.ptr(b), _lib.ptr(c), _lib.ptr(self.step_dev), 0, None,
+                                            0.0, 0.0, self.B, self.n_per, self.seed, off, self.elem_base, st),
+                   "b200_sde_update")
+        return n + 1
+
+    def _step_body(self, st, base_off):
+        """All launches of one PC step.  Noise offsets: (n_steps + 1) streams per step."""
+        n = 0
+        k = 0
+        if self.corr:
+            for _ in range(self.n_steps):
+                n += self._corrector(st, base_off + k)
+                k += 1
+        if self.pred:
+            n += self._predictor(st, base_off + k)
+        _lib.check(self.lib.b200_step_advance(_lib.ptr(self.step_dev), 1, st), "b200_step_advance")
+        return n + 1
+
+    # -- API --
+    def reset(self, x0=None):
+        self.step_dev.zero_()
+        self.step_host = 0
+        self.offset = 0
+        if x0 is not None:
+            self.x.copy_(x0)
+
+    def step(self):
+        """One PC step on the current stream.  Graph replay is not used when noise is injected or the Philox
+        offset must advance (offsets are baked into a captured graph), i.e. the graph path re-captures per offset
+        block; see `run`."""
+        st = _lib.stream()
+        n = self._step_body(st, self.offset)
+        self.offset += self.n_steps + 1
+        self.step_host += 1
+        self.launches_per_step = n
+        return n
+
+    def run(self, n_iters):
+        for _ in range(n_iters):
+            self.step()
+
+
+def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
+                   n_steps=1, probability_flow=False, continuous=False,
+                   denoise=True, eps=1e-3, device='cuda'):
+    """Create a Predictor-Corrector (PC) sampler (sampling.py:355-411).
+
+    Returns `pc_sampler(model) -> (samples, nfe)` with nfe = sde.N * (n_steps + 1) exactly as the reference reports
+    it (sampling.py:409).
+    """
+    predictor_update_fn = functools.partial(shared_predictor_update_fn, sde=sde, predictor=predictor,
+                                            probability_flow=probability_flow, continuous=continuous)
+    corrector_update_fn = functools.partial(shared_corrector_update_fn, sde=sde, corrector=corrector,
+                                            continuous=continuous, snr=snr, n_steps=n_steps)
+
+    def fusable(model):
+        return (isinstance(model, mutils.ScoreModel)
+                and (predictor is None or predictor in _BUILTIN_PREDICTORS)
+                and (corrector is None or corrector in _BUILTIN_CORRECTORS)
+                and isinstance(sde, (sde_lib.VPSDE, sde_lib.subVPSDE, sde_lib.VESDE)))
+
+    def prior(dev):
+        z = _noise(shape, dev)
+        if z is not None:
+            scale = sde.sigma_max if isinstance(sde, sde_lib.VESDE) else 1.0
+            return z * scale
+        return sde.prior_sampling(shape).to(dev)
+
+    def pc_sampler(model):
+        with torch.no_grad():
+            dev = torch.device(device) if not isinstance(model, mutils.ScoreModel) else model.engine.device
+            if fusable(model):
+                loop = FusedPCLoop(model, sde, shape, predictor, corrector, snr, n_steps, probability_flow,
+                                   continuous, eps)
+                with torch.cuda.device(dev):
+                    loop.reset(prior(dev))
+                    loop.run(sde.N)
+                    x = loop.x_mean if denoise else loop.x
+                    if loop.forwards_per_step == 0:
+                        x = loop.x
+                    return inverse_scaler(x.clone()), sde.N * (n_steps + 1)
+            # generic path: user-defined predictor/corrector classes around the engine
+            x = prior(dev)
+            timesteps = torch.linspace(sde.T, eps, sde.N, device=dev)
+            x_mean = x
+            for i in range(sde.N):
+                vec_t = torch.ones(shape[0], device=dev) * timesteps[i]
+                x, x_mean = corrector_update_fn(x, vec_t, model=model)
+                x, x_mean = predictor_update_fn(x, vec_t, model=model)
+            return inverse_scaler(x_mean if denoise else x), sde.N * (n_steps + 1)
+
+    return pc_sampler
+
+
+def get_ode_sampler(sde, shape, inverse_scaler, denoise=False, rtol=1e-5, atol=1e-5, method='RK45', eps=1e-3,
+                    device='cuda'):
+    """Probability-flow ODE sampler (sampling.py:414-485): scipy drives, the engine evaluates the drift."""
+    from scipy import integrate
+
+    def drift_fn(model, x, t):
+        score_fn = get_score_fn(sde, model, train=False, continuous=True)
+        return sde.reverse(score_fn, probability_flow=True).sde(x, t)[0]
+
+    def ode_sampler(model, z=None):
+        with torch.no_grad():
+            dev = model.engine.device if isinstance(model, mutils.ScoreModel) else torch.device(device)
+            x = sde.prior_sampling(shape).to(dev) if z is None else z
+
+            def ode_func(t, xf):
+                xt = mutils.from_flattened_numpy(xf, shape).to(dev).type(torch.float32)
+                vec_t = torch.ones(shape[0], device=dev) * t
+                return mutils.to_flattened_numpy(drift_fn(model, xt, vec_t))
+
+            sol = integrate.solve_ivp(ode_func, (sde.T, eps), mutils.to_flattened_numpy(x), rtol=rtol, atol=atol,
+                                      method=method)
+            x = torch.tensor(sol.y[:, -1]).reshape(shape).to(dev).type(torch.float32)
+            if denoise:
+                score_fn = get_score_fn(sde, model, train=False, continuous=True)
+                vec_eps = torch.ones(x.shape[0], device=dev) * eps
+                _, x = ReverseDiffusionPredictor(sde, score_fn, probability_flow=False).update_fn(x, vec_eps)
+            return inverse_scaler(x), sol.nfev
+
+    return ode_sampler

@@ -1,0 +1,202 @@
+"""Generates tests/golden/*.npz by running the UNMODIFIED reference (/root/reference) in the authoring container.
+
+TEST INFRASTRUCTURE ONLY.  Run:  python oracle/make_golden.py [--only NAME]
+Large tensors that are a pure function of a seed (weights, noise) are NOT stored: both sides regenerate them with
+`oracle/weights.py` / `noise_stream` and the fixture keeps a checksum to detect RNG drift.
+"""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle import ref_import, weights  # noqa: E402
+from b_pinn_kalman_filter_b200 import configs  # noqa: E402
+from b_pinn_kalman_filter_b200.models import utils as mutils  # noqa: E402
+import b_pinn_kalman_filter_b200.models  # noqa: E402,F401
+from b_pinn_kalman_filter_b200.models.engine import parameter_spec  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+# name -> (our config name, reference config module, overrides on both, B, labels)
+SCORE_CASES = {
+    "tiny_fourier_residual": ("test/tiny_ncsnpp", "configs.ve.cifar10_ncsnpp_continuous", {}, 3),
+    "tiny_output_skip": ("test/tiny_ncsnpp", "configs.ve.cifar10_ncsnpp_continuous",
+                         {"progressive": "output_skip", "progressive_input": "input_skip"}, 2),
+    "tiny_positional_vp": ("test/tiny_ncsnpp", "configs.vp.cifar10_ncsnpp_continuous",
+                           {"embedding_type": "positional", "scale_by_sigma": False, "_centered": True,
+                            "_sde": "vpsde"}, 2),
+    # resblock_type='ddpm' inside NCSN++ has no reference anchor: its Upsample(fir=True, with_conv=True) hits the
+    # broken upsample_conv_2d and Upsample(fir=False) calls F.interpolate(x, size, 'nearest') positionally, which
+    # torch >= 2 rejects (models/layerspp.py:117).
+    "cifar10_ncsnpp_ve": ("ve/cifar10_ncsnpp_continuous", "configs.ve.cifar10_ncsnpp_continuous", {}, 2),
+    "nc_ddpm_vp": ("vp/nc_ddpmpp", "configs.vp.nc_ddpmpp", {}, 1),
+}
+TINY = dict(nf=32, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=(8,))
+
+
+def tiny_pair(our_name, ref_module, over):
+    """(our config, reference config) with identical overrides."""
+    cfg = configs.get_config(our_name)
+    rcfg = ref_import.get_config(ref_module)
+    pairs = [cfg, rcfg]
+    if our_name.startswith("test/"):
+        for c in pairs:
+            c.model.update(TINY)
+            c.data.image_size = 16
+            c.training.sde = "vesde"
+            c.training.continuous = True
+            c.data.centered = False
+            c.model.scale_by_sigma = True
+            c.model.embedding_type = "fourier"
+            c.model.progressive, c.model.progressive_input = "none", "residual"
+            c.model.resblock_type = "biggan"
+            c.model.num_scales = 1000
+            c.model.sigma_max, c.model.sigma_min = 50, 0.01
+    for k, v in over.items():
+        for c in pairs:
+            if k == "_centered":
+                c.data.centered = v
+            elif k == "_sde":
+                c.training.sde = v
+            else:
+                c.model[k] = v
+    return cfg, rcfg
+
+
+def weight_checksum(sd):
+    s = 0.0
+    for k in sorted(sd):
+        s += float(sd[k].double().abs().sum())
+    return s
+
+
+def labels_for(cfg, B):
+    if cfg.model.embedding_type == "fourier":
+        return torch.tensor([0.05, 1.7, 40.0][:B], dtype=torch.float32)
+    return torch.tensor([3.0, 512.0, 998.0][:B], dtype=torch.float32)
+
+
+def noise_stream(seed, shape):
+    gen = torch.Generator().manual_seed(int(seed))
+    while True:
+        yield torch.randn(shape, generator=gen)
+
+
+def gen_score(ns, name):
+    our, refm, over, B = SCORE_CASES[name]
+    cfg, rcfg = tiny_pair(our, refm, over)
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    sd = weights.trained_like_state_dict(spec, cfg, seed=1234)
+    model = ns.mutils.create_model(rcfg)
+    model.load_state_dict({"module." + k: v for k, v in sd.items()})
+    model.eval()
+    g = torch.Generator().manual_seed(99)
+    S, C = cfg.data.image_size, cfg.data.num_channels
+    x = torch.rand(B, C, S, S, generator=g) * 1.5 - 0.25
+    lab = labels_for(cfg, B)
+    with torch.no_grad():
+        y = model(x, lab)
+    np.savez_compressed(os.path.join(GOLDEN, "score_%s.npz" % name), x=x.numpy(), labels=lab.numpy(), out=y.numpy(),
+                        weight_checksum=np.float64(weight_checksum(sd)), weight_seed=1234)
+    print("score", name, "out rms", float(y.pow(2).mean().sqrt()))
+
+
+PC_CASES = {
+    # name: (overrides, sde, predictor, corrector, snr, n_steps, continuous, N)
+    "ve_rd_langevin": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 12),
+    "ve_ancestral_ald": ({}, "vesde", "ancestral_sampling", "ald", 0.16, 2, True, 8),
+    "vp_em_none": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}, "vpsde",
+                   "euler_maruyama", "none", 0.16, 1, True, 10),
+    "vp_ancestral_langevin_discrete": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True},
+                                       "vpsde", "ancestral_sampling", "langevin", 0.2, 1, False, 10),
+    # (subVP + langevin/ald raises in the reference itself: subVPSDE has no `alphas`, sampling.py:269)
+    "subvp_rd_none": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}, "subvpsde",
+                      "reverse_diffusion", "none", 0.1, 1, True, 8),
+}
+
+
+def gen_pc(ns, name):
+    over, sde_name, pred, corr, snr, n_steps, continuous, N = PC_CASES[name]
+    cfg, rcfg = tiny_pair("test/tiny_ncsnpp", "configs.ve.cifar10_ncsnpp_continuous", over)
+    for c in (cfg, rcfg):
+        c.training.sde = sde_name
+        c.training.continuous = continuous
+    # the network keeps num_scales = 1000 (its `sigmas` buffer is indexed by labels up to 999, ncsnpp.py:245);
+    # only the SDE is shortened to N steps.
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    sd = weights.trained_like_state_dict(spec, cfg, seed=77)
+    model = ns.mutils.create_model(rcfg)
+    model.load_state_dict({"module." + k: v for k, v in sd.items()})
+    model.eval()
+    rcfg.model.num_scales = N
+    sde, eps = ref_import.get_sde(ns, rcfg)
+    B = 2
+    shape = (B, cfg.data.num_channels, cfg.data.image_size, cfg.data.image_size)
+    stream = noise_stream(4321, shape)
+    torch_randn_like = torch.randn_like
+    prior_orig = type(sde).prior_sampling
+    scale = cfg.model.sigma_max if sde_name == "vesde" else 1.0
+    try:
+        torch.randn_like = lambda t, **kw: next(stream).to(t.dtype)
+        type(sde).prior_sampling = lambda self, shp: next(stream) * scale
+        fn = ns.sampling.get_pc_sampler(sde, shape, ns.sampling.get_predictor(pred), ns.sampling.get_corrector(corr),
+                                        lambda v: v, snr, n_steps=n_steps, probability_flow=False,
+                                        continuous=continuous, denoise=True, eps=eps, device="cpu")
+        x, nfe = fn(model)
+    finally:
+        torch.randn_like = torch_randn_like
+        type(sde).prior_sampling = prior_orig
+    np.savez_compressed(os.path.join(GOLDEN, "pc_%s.npz" % name), out=x.numpy(), nfe=nfe,
+                        weight_checksum=np.float64(weight_checksum(sd)), weight_seed=77, noise_seed=4321)
+    print("pc", name, "out rms", float(x.pow(2).mean().sqrt()), "nfe", nfe)
+
+
+def gen_ops(ns):
+    g = torch.Generator().manual_seed(5)
+    cases = {}
+    k1 = torch.tensor([1., 3., 3., 1.])
+    k = torch.outer(k1, k1)
+    k = k / k.sum()
+    for tag, (shape, kk, up, down, pad) in {
+        "down2": ((2, 3, 16, 16), k, 1, 2, (1, 1)),
+        "up2": ((2, 3, 8, 8), k * 4, 2, 1, (2, 1)),
+        "pad22": ((1, 4, 9, 9), k, 1, 1, (2, 2)),
+        "odd": ((1, 2, 7, 5), torch.rand(3, 5, generator=g), 3, 2, (1, 2)),
+        "crop": ((1, 2, 10, 10), k, 1, 1, (-1, 0)),
+    }.items():
+        x = torch.randn(shape, generator=g)
+        y = ns.upfirdn2d_mod.upfirdn2d_native(x, kk, up, up, down, down, pad[0], pad[1], pad[0], pad[1])
+        cases["ufd_%s_x" % tag], cases["ufd_%s_k" % tag], cases["ufd_%s_y" % tag] = x.numpy(), kk.numpy(), y.numpy()
+        cases["ufd_%s_cfg" % tag] = np.array([up, down, pad[0], pad[1]])
+    x = torch.randn(2, 6, 5, 5, generator=g)
+    b = torch.randn(6, generator=g)
+    cases["lrelu_x"], cases["lrelu_b"] = x.numpy(), b.numpy()
+    cases["lrelu_y"] = ns.fused_act_mod.fused_leaky_relu(x, b).numpy()   # CPU branch: slope fixed at 0.2
+    np.savez_compressed(os.path.join(GOLDEN, "ops.npz"), **cases)
+    print("ops", len(cases))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--only", default=None)
+    a = ap.parse_args()
+    os.makedirs(GOLDEN, exist_ok=True)
+    ns = ref_import.load()
+    torch.manual_seed(0)
+    if a.only in (None, "ops"):
+        gen_ops(ns)
+    for n in SCORE_CASES:
+        if a.only in (None, "score", n):
+            gen_score(ns, n)
+    for n in PC_CASES:
+        if a.only in (None, "pc", n):
+            gen_pc(ns, n)
+
+
+if __name__ == "__main__":
+    main()
