@@ -112,7 +112,9 @@ PC_CASES = {
     "ve_ancestral_ald": ({}, "vesde", "ancestral_sampling", "ald", 0.16, 2, True, 8),
     "vp_em_none": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}, "vpsde",
                    "euler_maruyama", "none", 0.16, 1, True, 10),
-    "vp_ancestral_langevin_discrete": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True},
+    # beta_max = 5: with N = 10 the default beta_max = 20 gives discrete betas > 1 and the reference itself returns NaN
+    "vp_ancestral_langevin_discrete": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True,
+                                        "beta_max": 5.0},
                                        "vpsde", "ancestral_sampling", "langevin", 0.2, 1, False, 10),
     # (subVP + langevin/ald raises in the reference itself: subVPSDE has no `alphas`, sampling.py:269)
     "subvp_rd_none": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}, "subvpsde",

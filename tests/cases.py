@@ -1,0 +1,117 @@
+"""Our-side construction of the golden cases of oracle/make_golden.py (no reference needed at test time).
+
+make_golden.py builds (our config, reference config) pairs with identical overrides and runs the reference; the
+tests rebuild only our half, regenerate the seeded weights / inputs / noise and compare with the stored outputs.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from oracle import weights  # noqa: E402
+from b_pinn_kalman_filter_b200 import configs  # noqa: E402
+from b_pinn_kalman_filter_b200.models import utils as mutils  # noqa: E402
+import b_pinn_kalman_filter_b200.models  # noqa: E402,F401
+from b_pinn_kalman_filter_b200.models.engine import parameter_spec  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+SCORE_CASES = {
+    "tiny_fourier_residual": ("test/tiny_ncsnpp", {}, 3),
+    "tiny_output_skip": ("test/tiny_ncsnpp", {"progressive": "output_skip", "progressive_input": "input_skip"}, 2),
+    "tiny_positional_vp": ("test/tiny_ncsnpp", {"embedding_type": "positional", "scale_by_sigma": False,
+                                                "_centered": True, "_sde": "vpsde"}, 2),
+    "cifar10_ncsnpp_ve": ("ve/cifar10_ncsnpp_continuous", {}, 2),
+    "nc_ddpm_vp": ("vp/nc_ddpmpp", {}, 1),
+}
+TINY = dict(nf=32, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=(8,))
+
+_POS = {"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}
+PC_CASES = {
+    # name: (overrides, sde, predictor, corrector, snr, n_steps, continuous, N)
+    "ve_rd_langevin": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 12),
+    "ve_ancestral_ald": ({}, "vesde", "ancestral_sampling", "ald", 0.16, 2, True, 8),
+    "vp_em_none": (_POS, "vpsde", "euler_maruyama", "none", 0.16, 1, True, 10),
+    "vp_ancestral_langevin_discrete": (dict(_POS, beta_max=5.0), "vpsde", "ancestral_sampling", "langevin", 0.2, 1, False, 10),
+    "subvp_rd_none": (_POS, "subvpsde", "reverse_diffusion", "none", 0.1, 1, True, 8),
+}
+
+
+def our_config(our_name, over):
+    c = configs.get_config(our_name)
+    if our_name.startswith("test/"):
+        c.model.update(TINY)
+        c.data.image_size = 16
+        c.training.sde = "vesde"
+        c.training.continuous = True
+        c.data.centered = False
+        c.model.scale_by_sigma = True
+        c.model.embedding_type = "fourier"
+        c.model.progressive, c.model.progressive_input = "none", "residual"
+        c.model.resblock_type = "biggan"
+        c.model.num_scales = 1000
+        c.model.sigma_max, c.model.sigma_min = 50, 0.01
+    for k, v in over.items():
+        if k == "_centered":
+            c.data.centered = v
+        elif k == "_sde":
+            c.training.sde = v
+        else:
+            c.model[k] = v
+    return c
+
+
+def weight_checksum(sd):
+    return sum(float(sd[k].double().abs().sum()) for k in sorted(sd))
+
+
+def state_dict_for(cfg, seed):
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    return weights.trained_like_state_dict(spec, cfg, seed=seed)
+
+
+def score_case(name):
+    """-> (cfg, state_dict, x, labels, golden_out)"""
+    our, over, B = SCORE_CASES[name]
+    cfg = our_config(our, over)
+    g = np.load(os.path.join(GOLDEN, "score_%s.npz" % name))
+    sd = state_dict_for(cfg, int(g["weight_seed"]))
+    assert abs(weight_checksum(sd) - float(g["weight_checksum"])) <= 1e-9 * float(g["weight_checksum"]), \
+        "seeded weights drifted from the ones the golden vectors were made with"
+    return cfg, sd, torch.from_numpy(g["x"]), torch.from_numpy(g["labels"]), torch.from_numpy(g["out"])
+
+
+def noise_stream(seed, shape):
+    gen = torch.Generator().manual_seed(int(seed))
+    while True:
+        yield torch.randn(shape, generator=gen)
+
+
+def pc_case(name):
+    """-> dict(cfg, sd, shape, sde_name, pred, corr, snr, n_steps, continuous, N, eps, out, nfe, noise_seed)"""
+    over, sde_name, pred, corr, snr, n_steps, continuous, N = PC_CASES[name]
+    cfg = our_config("test/tiny_ncsnpp", over)
+    cfg.training.sde = sde_name
+    cfg.training.continuous = continuous
+    g = np.load(os.path.join(GOLDEN, "pc_%s.npz" % name))
+    sd = state_dict_for(cfg, int(g["weight_seed"]))
+    assert abs(weight_checksum(sd) - float(g["weight_checksum"])) <= 1e-9 * float(g["weight_checksum"])
+    shape = (2, cfg.data.num_channels, cfg.data.image_size, cfg.data.image_size)
+    return dict(cfg=cfg, sd=sd, shape=shape, sde_name=sde_name, pred=pred, corr=corr, snr=snr, n_steps=n_steps,
+                continuous=continuous, N=N, eps=1e-5 if sde_name == "vesde" else 1e-3,
+                out=torch.from_numpy(g["out"]), nfe=int(g["nfe"]), noise_seed=int(g["noise_seed"]))
+
+
+def rel_l2(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def max_rel(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))

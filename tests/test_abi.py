@@ -31,7 +31,6 @@ def test_library_exports_every_declared_symbol():
 def test_python_binding_table_matches_header():
     from b_pinn_kalman_filter_b200 import _lib
     import b_pinn_kalman_filter_b200.models.engine  # noqa: F401  registers the engine entry points
-    import b_pinn_kalman_filter_b200.op.grid_sample  # noqa: F401
     declared = set(_declared())
     bound = set(_lib._SIGNATURES)
     assert bound <= declared, sorted(bound - declared)
