@@ -23,14 +23,12 @@ struct GnArgs {
 // thread always owns the same 8 channels (cv = tid % CV) and steps over pixels.
 template <typename T>
 __global__ void __launch_bounds__(256) gn_partial_kernel(GnArgs a) {
-  extern __shared__ float sh[];  // [C] sums, [C] sumsq
+  extern __shared__ float sh[];  // [ppt][2C] per-thread partials (fixed-order fold: bit-reproducible, no atomics)
   const int C = a.C1 + a.C2, CV = C >> 3;
   const int b = blockIdx.x / a.nsplit, sp = blockIdx.x % a.nsplit;
   const int ppt = blockDim.x / CV;              // pixels per sweep
   const int cv = threadIdx.x % CV, pl = threadIdx.x / CV;
   const int c0 = cv << 3;
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.0f;
-  __syncthreads();
   const int per = (a.HW + a.nsplit - 1) / a.nsplit;
   const int p_begin = sp * per, p_end = min(a.HW, p_begin + per);
   const T* src; int cs, cc;
@@ -46,7 +44,13 @@ __global__ void __launch_bounds__(256) gn_partial_kernel(GnArgs a) {
     for (int j = 0; j < 8; ++j) { s[j] += v[j]; q[j] = fmaf(v[j], v[j], q[j]); }
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) { atomicAdd(&sh[c0 + j], s[j]); atomicAdd(&sh[C + c0 + j], q[j]); }
+  for (int j = 0; j < 8; ++j) { sh[pl * 2 * C + c0 + j] = s[j]; sh[pl * 2 * C + C + c0 + j] = q[j]; }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
+    float t = 0.f;
+    for (int r = 0; r < ppt; ++r) t += sh[r * 2 * C + i];
+    sh[i] = t;   // row 0 is only read by this thread's own column here
+  }
   __syncthreads();
   const int cpg = C / a.G;
   for (int g = threadIdx.x; g < a.G; g += blockDim.x) {
@@ -142,7 +146,7 @@ extern "C" int b200_gn_partial(const void* x1, int C1, const void* x2, int C2, i
   int rc = gn_fill(a, x1, C1, x2, C2, B, HW, G, nsplit, partial);
   if (rc || B == 0) return rc;
   const int C = C1 + C2, thr = gn_threads(C);
-  const size_t smem = 2 * C * sizeof(float);
+  const size_t smem = (size_t)(thr / (C / 8)) * 2 * C * sizeof(float);   // <= 256 * 16 * 4 = 16 KB
   if (dtype == B200_DT_F32) gn_partial_kernel<float><<<B * nsplit, thr, smem, st>>>(a);
   else if (dtype == B200_DT_BF16) gn_partial_kernel<bf16><<<B * nsplit, thr, smem, st>>>(a);
   else return B200_ERR_ARG;

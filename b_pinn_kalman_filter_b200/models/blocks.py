@@ -67,12 +67,12 @@ class Net:
                b.sample_mul.data_ptr(), B)
         plan.temb_op_index = len(plan.ops) - 1
         b.emit("b200_linear_f32", emb.data_ptr(), e.dev(self.lin0 + ".weight"), e.dev(self.lin0 + ".bias"),
-               t1.data_ptr(), B, embed_dim, 4 * nf, 0, 0)
+               t1.data_ptr(), B, embed_dim, 4 * nf, 0, 0, flops=2 * B * embed_dim * 4 * nf)
         b.emit("b200_linear_f32", t1.data_ptr(), e.dev(self.lin1 + ".weight"), e.dev(self.lin1 + ".bias"),
-               t2.data_ptr(), B, 4 * nf, 4 * nf, 1, 0)
+               t2.data_ptr(), B, 4 * nf, 4 * nf, 1, 0, flops=2 * B * 16 * nf * nf)
         wcat, bcat = e.packed_dense()
         b.emit("b200_linear_f32", t2.data_ptr(), wcat.data_ptr(), bcat.data_ptr(), b.temb_all.data_ptr(), B, 4 * nf,
-               total, 1, 0)
+               total, 1, 0, flops=2 * B * 4 * nf * total)
 
     def dense(self, prefix, out_ch):
         """Registers a block's Dense_0 and returns its column offset in the batched projection."""

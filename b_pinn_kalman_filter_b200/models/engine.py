@@ -97,6 +97,30 @@ class Plan:
         self.labels = None     # fp32 [B]
         self.out = None        # fp32 NCHW output
         self.launches = 0
+        self.meta = []         # per launch: (entry point, algorithmic FLOPs) -- what bench.py's roofline is computed from
+
+    def flops(self, prefix=None):
+        return sum(f for n, f in self.meta if prefix is None or n.startswith(prefix))
+
+    def run_timed(self, stream_ptr):
+        """Runs the plan with a CUDA-event pair around every launch (on the launching stream); returns
+        {entry point: (launches, total ms, total FLOPs)}.  Measurement aid for bench.py, not used while sampling."""
+        evs = []
+        stream = torch.cuda.current_stream()
+        for fn, args, name in self.ops:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            rc = fn(*args, stream_ptr)
+            e1.record(stream)
+            if rc != 0:
+                _lib.check(rc, name)
+            evs.append((e0, e1))
+        stream.synchronize()
+        out = {}
+        for (e0, e1), (name, fl) in zip(evs, self.meta):
+            n, ms, f = out.get(name, (0, 0.0, 0))
+            out[name] = (n + 1, ms + e0.elapsed_time(e1), f + fl)
+        return out
 
     def run(self, stream_ptr):
         for fn, args, name in self.ops:
@@ -173,9 +197,10 @@ class Builder:
         self.plan.keep.append(t)
         return t
 
-    def emit(self, name, *args):
+    def emit(self, name, *args, flops=0):
         fn = getattr(self.lib, name)
         self.plan.ops.append((fn, args, name))
+        self.plan.meta.append((name, int(flops)))
 
     # ---- primitives -------------------------------------------------------------------------------------------
     def gn(self, x, key, groups, act, x2=None):
@@ -227,7 +252,8 @@ class Builder:
             self.emit("b200_conv2d_simt", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, self.temb_stride,
                       res, out_scale, nchw_out.data_ptr(), 1,
                       self.sample_mul.data_ptr() if self.sample_mul is not None else None, self.dt, self.B, x.H, x.W,
-                      Ho, Wo, cout, ksize, ksize, stride, pad[0], pad[1])
+                      Ho, Wo, cout, ksize, ksize, stride, pad[0], pad[1],
+                      flops=2 * self.B * Ho * Wo * cout * cin_true * ksize * ksize)
             return None
         self.e.emit_conv(self, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, stride, pad, key)
         return out
@@ -398,7 +424,13 @@ class ScoreEngine:
         p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
         b.emit("b200_conv2d_simt", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, b.temb_stride,
                res, out_scale, out, 0, None, self.dt, b.B, x.H, x.W, out.H, out.W,
-               out.C, ksize, ksize, stride, pad[0], pad[1])
+               out.C, ksize, ksize, stride, pad[0], pad[1], flops=self.conv_flops(b, x, x2, out, ksize))
+
+    @staticmethod
+    def conv_flops(b, x, x2, out, ksize):
+        """Algorithmic FLOPs (2 MAC) over the channels that carry data (padding lanes do not count)."""
+        cin = x.Ct + (x2.Ct if x2 is not None else 0)
+        return 2 * b.B * out.H * out.W * out.Ct * cin * ksize * ksize
 
     def emit_attention(self, b, qkv, out, L, C, es):
         from . import tc
@@ -406,7 +438,7 @@ class ScoreEngine:
             tc.emit_attention(b, qkv, out, L, C)
             return
         b.emit("b200_attention_simt", qkv, qkv.at(C * es), qkv.at(2 * C * es), out, self.dt, b.B, L, C, 3 * C, 3 * C,
-               3 * C, C, float(int(C) ** (-0.5)))
+               3 * C, C, float(int(C) ** (-0.5)), flops=4 * b.B * L * L * C)
 
     # ---- plans ------------------------------------------------------------------------------------------------
     def plan(self, B):

@@ -93,9 +93,18 @@ class ScoreModel:
             self.init_weights(config.seed if seed is None else seed)
 
     # -- parameters --
-    def init_weights(self, seed):
+    def init_weights(self, seed, zero_init_scale=None):
+        """Random init with the reference's distributions.  `zero_init_scale`: replaces the 1e-10 scale of the
+        `init_scale=0.` layers (models/layers.py:83-86) -- with it left at 1e-10 the score is ~0 and the Langevin
+        step size (sampling.py:278) overflows, so throughput runs on random weights pass 1.0 here."""
         gen = torch.Generator().manual_seed(int(seed))
-        sd = {key: init_tensor(shape, init, gen) for key, shape, init in self.engine.spec()}
+
+        def fix(init):
+            if zero_init_scale is not None and isinstance(init, tuple) and init[0] == "default" and init[1] == 0:
+                return ("default", zero_init_scale)
+            return init
+
+        sd = {key: init_tensor(shape, fix(init), gen) for key, shape, init in self.engine.spec()}
         sd["sigmas"] = torch.tensor(get_sigmas(self.config), dtype=torch.float32)
         self.engine.params["sigmas"] = sd["sigmas"].to(self.engine.device)
         self.engine.load_state_dict(sd)

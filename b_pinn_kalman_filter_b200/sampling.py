@@ -532,8 +532,13 @@ class FusedPCLoop:
 
 def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
                    n_steps=1, probability_flow=False, continuous=False,
-                   denoise=True, eps=1e-3, device='cuda'):
+                   denoise=True, eps=1e-3, device='cuda', process_group=None, rank_offset=0, total_batch=None):
     """Create a Predictor-Corrector (PC) sampler (sampling.py:355-411).
+
+    Beyond the reference's arguments: `process_group` / `rank_offset` / `total_batch` describe a batch-sharded run
+    (one process per GPU): `shape[0]` is this rank's shard, `rank_offset` its first global sample index (decorrelates
+    the Philox streams) and the Langevin batch-mean norms are all-reduced over the group so that the step size is the
+    one the unsharded batch would get (sampling.py:276-278).
 
     Returns `pc_sampler(model) -> (samples, nfe)` with nfe = sde.N * (n_steps + 1) exactly as the reference reports
     it (sampling.py:409).
@@ -561,7 +566,8 @@ def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
             dev = torch.device(device) if not isinstance(model, mutils.ScoreModel) else model.engine.device
             if fusable(model):
                 loop = FusedPCLoop(model, sde, shape, predictor, corrector, snr, n_steps, probability_flow,
-                                   continuous, eps)
+                                   continuous, eps, process_group=process_group, rank_offset=rank_offset,
+                                   total_batch=total_batch)
                 with torch.cuda.device(dev):
                     loop.reset(prior(dev))
                     loop.run(sde.N)

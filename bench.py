@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py -- the reference's headline metric on B200: PC samples/s of the CIFAR-10-shape NCSN++ VE-SDE
+predictor-corrector sampler (ReverseDiffusion + Langevin, 1000 steps; BASELINE.json configs[2]).
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run)
+    python bench.py --impl reference ...                      (CPU arm: the oracle port of the reference's path)
+
+A "step" is one PC step of the whole batch = Langevin corrector (1 score-net forward + norm pass + update) followed
+by the reverse-diffusion predictor (1 forward + update): 2 score-network forwards.  Every PC step costs the same, so
+`value` = batch / (measured seconds per PC step x 1000 steps); K steps are timed after W warm-up steps, on the
+device, max over ranks.  `e2e` runs the public API call a user makes -- `sampling.get_pc_sampler(...)(model)` --
+with the prior drawn on the host (pinned) and copied in, and the samples copied back out, inside the timed region.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_STEPS = 1000                     # sde.N of configs/ve/cifar10_ncsnpp_continuous.py
+CONFIG = "ve/cifar10_ncsnpp_continuous"
+TOTAL_BATCH = 1024                 # BASELINE.json configs[2]
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch-per-gpu", type=int, default=0, help="default: 1024 at N=1, 1024/N otherwise ... see --scaling")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every GPU samples --batch-per-gpu (default 1024) images; strong: 1024 images total")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--e2e-steps", type=int, default=0, help="PC steps of the end-to-end API run (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-aux", action="store_true", help="skip the upfirdn2d / ns_step side measurements")
+    ap.add_argument("--cpu-batch", type=int, default=8)
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, power, reasons = [], 0, [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [v.strip() for v in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); smax = max(smax, float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax or None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm": d["hbm_gbs"], "tc_burst": d["bf16_tflops"], "tc_sustained": d["bf16_tflops_sustained"],
+                "source": "measured"}
+    return {"hbm": 6650.0, "tc_burst": 1590.0, "tc_sustained": 1400.0, "source": "fallback"}
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's path (oracle/score_net_ref.py + oracle/sampling_ref.py), torch CPU fp32
+# ------------------------------------------------------------------------------------------------------------------
+def cpu_pc_steps(batch, n_pc_steps, threads):
+    """Times `n_pc_steps` PC steps (Langevin + reverse diffusion, 2 forwards each) of the C3 workload on the host.
+    Returns (seconds per PC step, batch)."""
+    import torch
+    from oracle import sampling_ref, score_net_ref, weights
+    from b_pinn_kalman_filter_b200 import configs
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    import b_pinn_kalman_filter_b200.models  # noqa: F401
+    from b_pinn_kalman_filter_b200.models.engine import parameter_spec
+    torch.set_num_threads(threads)
+    cfg = configs.get_config(CONFIG)
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    sd = weights.trained_like_state_dict(spec, cfg, seed=42)
+    net = score_net_ref.RefScoreNet(cfg, sd)
+    sde = sampling_ref.RefSDE.from_config(cfg)
+    shape = (batch, 3, 32, 32)
+    gen = torch.Generator().manual_seed(0)
+
+    def noises():
+        while True:
+            yield torch.randn(shape, generator=gen)
+
+    with torch.no_grad():
+        sampling_ref.pc_sample(sde, net, shape, "reverse_diffusion", "langevin", 0.16, 1, True, noises(), eps=1e-5,
+                               n_iters=1)                                       # warm-up
+        t0 = time.perf_counter()
+        sampling_ref.pc_sample(sde, net, shape, "reverse_diffusion", "langevin", 0.16, 1, True, noises(), eps=1e-5,
+                               n_iters=n_pc_steps)
+        dt = time.perf_counter() - t0
+    return dt / n_pc_steps, batch
+
+
+def cpu_baseline_obj(batch, n_pc_steps):
+    threads = os.cpu_count() or 1
+    s_per_step, b = cpu_pc_steps(batch, n_pc_steps, threads)
+    return {"value": b / (s_per_step * N_STEPS), "unit": "samples/s", "cores": threads, "kind": "port",
+            "sample": "%d PC steps (2 score-net forwards each) at batch %d of the same 1000-step workload, torch %s CPU "
+                      "fp32 oracle port; per-step time x 1000" % (n_pc_steps, b, __import__("torch").__version__),
+            "s_per_pc_step": s_per_step}
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, a.steps)
+    warm = a.warmup
+    t0 = time.perf_counter()
+    s_per_step, b = cpu_pc_steps(a.cpu_batch, min(steps, 4), os.cpu_count() or 1)
+    val = b / (s_per_step * N_STEPS)
+    line = {"impl": "reference", "metric": "PC samples/s (NCSN++ 32x32, 1000 steps)", "value": val, "unit": "samples/s",
+            "n_gpus": a.gpus, "steps": a.steps, "warmup": warm, "ms_per_step": s_per_step * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C3 cifar10 NCSN++ VE PC sampler (reverse_diffusion + langevin, snr 0.16), N=1000",
+                       "batch": b, "timed_pc_steps": min(steps, 4)},
+            "cpu_baseline": {"value": val, "unit": "samples/s", "cores": os.cpu_count() or 1, "kind": "port",
+                             "sample": "%d PC steps at batch %d on the host, per-step time x 1000" % (min(steps, 4), b)},
+            "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------------------------
+def aux_measurements(dev, pk):
+    """The metric's second half (upfirdn2d HBM GB/s at the C5 shape) and the ns_step rollout (configs[1]); each is
+    one kernel timed alone with CUDA events on the launching stream, inputs (>= 268 MB) larger than L2."""
+    import torch
+    from b_pinn_kalman_filter_b200 import op
+    from b_pinn_kalman_filter_b200.op import ns_step
+    out = {}
+
+    def timeit(fn, iters=10):
+        for _ in range(3):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    k1 = torch.tensor([1., 3., 3., 1.], device=dev)
+    k = torch.outer(k1, k1)
+    k = k / k.sum()
+    x = torch.randn(8, 128, 256, 256, device=dev)
+    from b_pinn_kalman_filter_b200.op.upfirdn2d import _launch
+    xp = x.view(-1, 256, 256)
+    for tag, fn, nbytes in [
+        ("down2 [8x128,256,256]->[.,128,128] f32 planes", lambda: _launch(xp, k, (1, 1), (2, 2), (1, 1, 1, 1)),
+         4 * (x.numel() + x.numel() // 4)),
+    ]:
+        ms = timeit(fn)
+        out["upfirdn2d"] = {"shape": tag, "ms": ms, "achieved": nbytes / ms / 1e6, "peak": pk["hbm"], "unit": "GB/s",
+                            "frac": nbytes / ms / 1e6 / pk["hbm"], "algorithmic_bytes": nbytes}
+    xs = torch.randn(8, 128, 128, 128, device=dev).view(-1, 128, 128)
+    ms = timeit(lambda: _launch(xs, k * 4, (2, 2), (1, 1), (2, 1, 2, 1)))
+    nb = 4 * (xs.numel() * 5)
+    out["upfirdn2d_up2"] = {"shape": "up2 [8x128,128,128]->[.,256,256] f32 planes", "ms": ms,
+                            "achieved": nb / ms / 1e6, "peak": pk["hbm"], "unit": "GB/s", "frac": nb / ms / 1e6 / pk["hbm"]}
+    del x, xp, xs
+    # ns_step: B=256, 192x192 (pinn_kalman/simulator.py:35-61): velocity -> pressure -> density
+    B, S = 256, 192
+    g = torch.Generator(device="cpu").manual_seed(0)
+    vel = ((torch.rand(B, 2, S, S, generator=g) * 0.75 + 0.05) * torch.where(torch.rand(B, 2, S, S, generator=g) > 0.5, 1.0, -1.0)).to(dev)
+    pres = (torch.rand(B, 1, S, S, generator=g) * 0.1).to(dev)
+    dens = (torch.rand(B, 1, S, S, generator=g) * 0.5 + 0.25).to(dev)
+    dt, dx = 0.0025, 1 / 200
+
+    def step():
+        v = ns_step.update_velocity(vel, pres, dt, dx)
+        p = ns_step.update_pressure(pres, v, dt, dx)
+        ns_step.update_density(dens, v, dt, dx)
+        return p
+
+    ms = timeit(step)
+    cells = B * S * S
+    out["ns_step"] = {"shape": "B=256 192x192 fp32, velocity+pressure+density", "ms_per_step": ms,
+                      "cell_updates_per_s": cells / ms * 1e3, "achieved": 52 * cells / ms / 1e6, "peak": pk["hbm"],
+                      "unit": "GB/s", "frac": 52 * cells / ms / 1e6 / pk["hbm"],
+                      "algorithmic_bytes_per_cell": 52}
+    return out
+
+
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    from b_pinn_kalman_filter_b200 import _lib, configs, sampling, sde_lib
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    import b_pinn_kalman_filter_b200.models  # noqa: F401
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()
+    pk = peaks()
+
+    B = a.batch_per_gpu or (TOTAL_BATCH if a.scaling == "weak" else TOTAL_BATCH // world)
+    cfg = configs.get_config(CONFIG)
+    cfg.device = dev
+    model = mutils.ScoreModel(cfg, device=dev, precision=a.precision, init=False)
+    model.init_weights(42, zero_init_scale=1.0)     # random-init weights of the named architecture (see init_weights)
+    sde = sde_lib.VESDE(cfg.model.sigma_min, cfg.model.sigma_max, cfg.model.num_scales)
+    shape = (B, 3, 32, 32)
+    pg = dist.group.WORLD if world > 1 else None
+    loop = sampling.FusedPCLoop(model, sde, shape, sampling.ReverseDiffusionPredictor, sampling.LangevinCorrector,
+                                cfg.sampling.snr, cfg.sampling.n_steps_each, False, True, 1e-5, process_group=pg,
+                                rank_offset=rank * B, total_batch=B * world, seed=1234)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing: W warm-up + K timed PC steps -------------------------------------------------
+    x0 = torch.randn(shape, device=dev) * sde.sigma_max
+    loop.reset(x0)
+    for _ in range(a.warmup):
+        loop.step()
+    barrier()
+    clocks = ClockSampler(local)
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    launches = 0
+    for _ in range(a.steps):
+        launches += loop.step()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    finite = bool(torch.isfinite(loop.x).all())
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_per_step = float(t.item()) / a.steps
+    total_B = B * world
+    value = total_B / (ms_per_step * 1e-3 * N_STEPS)
+
+    # ---- per-kernel breakdown of one score-net forward (CUDA events around every launch) -----------------------
+    plan = loop.plan
+    torch.cuda.synchronize()
+    table = plan.run_timed(_lib.stream())
+    fwd_ms = sum(v[1] for v in table.values())
+    conv_names = [n for n in table if "conv" in n or "gemm" in n]
+    top = max(table, key=lambda n: table[n][1])
+    dom = max(conv_names, key=lambda n: table[n][1]) if conv_names else top
+    n_l, d_ms, d_fl = table[dom]
+    achieved = d_fl / (d_ms * 1e-3) / 1e12 if d_ms > 0 else 0.0
+    roof = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tc_sustained"], "unit": "TFLOP/s",
+            "frac": achieved / pk["tc_sustained"], "traffic": None, "peak_source": pk["source"] + " (sustained bf16)",
+            "launches_per_forward": n_l, "avg_launch_ms": d_ms / max(n_l, 1),
+            "flops_per_forward": d_fl, "share_of_forward": d_ms / fwd_ms if fwd_ms else None}
+    breakdown = {n: {"launches": v[0], "ms": round(v[1], 4), "gflop": round(v[2] / 1e9, 3)} for n, v in
+                 sorted(table.items(), key=lambda kv: -kv[1][1])}
+
+    # ---- end to end through the public API with host buffers ---------------------------------------------------
+    e2e_steps = a.e2e_steps or N_STEPS
+    est = ms_per_step * 1e-3 * e2e_steps
+    if not a.e2e_steps and est > 150.0:
+        e2e_steps = max(a.steps, int(150.0 / (ms_per_step * 1e-3)))
+    sde_e = sde_lib.VESDE(cfg.model.sigma_min, cfg.model.sigma_max, e2e_steps)
+    host_prior = torch.empty(shape, dtype=torch.float32).pin_memory()
+    host_prior.normal_(generator=torch.Generator().manual_seed(rank)).mul_(sde.sigma_max)
+    host_out = torch.empty(shape, dtype=torch.float32).pin_memory()
+    sde_e.prior_sampling = lambda shp: host_prior            # the API draws the prior on the host (sde_lib.py:290)
+    fn = sampling.get_pc_sampler(sde_e, shape, sampling.ReverseDiffusionPredictor, sampling.LangevinCorrector,
+                                 lambda v: v, cfg.sampling.snr, n_steps=cfg.sampling.n_steps_each, continuous=True,
+                                 denoise=True, eps=1e-5, device=dev, process_group=pg, rank_offset=rank * B,
+                                 total_batch=total_B)
+    barrier()
+    t0 = time.perf_counter()
+    xs, nfe = fn(model)
+    host_out.copy_(xs, non_blocking=True)
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    e2e_val = total_B / (e2e_s / e2e_steps * N_STEPS)
+    e2e_finite = bool(torch.isfinite(host_out).all())
+    nbytes = host_prior.numel() * 4
+
+    line = {"metric": "PC samples/s (NCSN++ 32x32, 1000 steps)", "value": value, "unit": "samples/s", "n_gpus": world,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": a.scaling, "vs_baseline": None, "dtype": a.precision, "data": "synthetic",
+            "config": {"workload": "C3: cifar10 NCSN++ (62.8M params) VE-SDE PC sampler, reverse_diffusion + langevin, "
+                                   "snr 0.16, N=1000, 3x32x32", "batch_per_gpu": B, "global_batch": total_B,
+                       "pc_steps_per_sample": N_STEPS, "forwards_per_pc_step": loop.forwards_per_step,
+                       "value_definition": "global_batch / (measured s per PC step x 1000 PC steps)",
+                       "l2": "activations per forward (>1 GB) exceed the 126 MB L2; no flush needed",
+                       "weights": "random init seed 42 (init_scale=0 layers drawn at scale 1), Philox noise on device",
+                       "parallelism": "dp%d (batch shards, 8-byte all-reduce per Langevin step)" % world},
+            "score_evals_per_s": total_B * loop.forwards_per_step / (ms_per_step * 1e-3),
+            "model_tflops": plan.flops() * loop.forwards_per_step * world / (ms_per_step * 1e-3) / 1e12,
+            "gpu_launches": launches, "finite": finite and e2e_finite,
+            "clocks": clk, "roofline": roof, "forward_breakdown": breakdown, "forward_ms_sum_of_kernels": fwd_ms,
+            "e2e": {"value": e2e_val, "unit": "samples/s", "h2d_bytes_per_step": nbytes / e2e_steps,
+                    "d2h_bytes_per_step": nbytes / e2e_steps, "h2d_bytes_total": nbytes, "d2h_bytes_total": nbytes,
+                    "pc_steps_run": e2e_steps, "seconds": e2e_s, "nfe": nfe,
+                    "api": "sampling.get_pc_sampler(VESDE(N=%d), ...)(model): pinned-host prior -> H2D, %d PC steps, "
+                           "samples -> D2H; scaled to 1000 steps" % (e2e_steps, e2e_steps)}}
+    if rank == 0:
+        if not a.no_aux:
+            line["aux"] = aux_measurements(dev, pk)
+        if not a.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline_obj(a.cpu_batch, 2)
+        elif not a.no_cpu_baseline:
+            line["cpu_baseline"] = {"value": None, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
+                                    "sample": "timed at N=1 only"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

@@ -82,14 +82,15 @@ def test_upfirdn2d_backward_is_adjoint(cuda):
     for up, down, pad in [(1, 2, (1, 1)), (2, 1, (2, 1)), (1, 1, (2, 2))]:
         x = torch.randn(2, 3, 12, 12, device=cuda, requires_grad=True)
         y = op.upfirdn2d(x, k * up * up, up, down, pad)
-        g = torch.randn_like(y)
+        g = torch.randn_like(y).requires_grad_()
         (gx,) = torch.autograd.grad(y, x, g, create_graph=True)
         lhs = float((y.detach().double() * g.double()).sum())
         rhs = float((x.detach().double() * gx.detach().double()).sum())
         assert abs(lhs - rhs) <= 1e-4 * max(1.0, abs(lhs))
-        # reference oracle for the gradient: autograd through F.conv2d restatement on CPU in fp64
-        gx.sum().backward()
-        assert x.grad is not None and torch.isfinite(x.grad).all()
+        # double backward (op/upfirdn2d.py:62-85): d<gx, w>/dg is the forward op applied to w
+        w = torch.randn_like(x)
+        (gg,) = torch.autograd.grad(gx, g, w)
+        torch.testing.assert_close(gg, op.upfirdn2d(w, k * up * up, up, down, pad), rtol=1e-5, atol=1e-5)
 
 
 def test_upfirdn2d_rejects_cpu_tensor():
