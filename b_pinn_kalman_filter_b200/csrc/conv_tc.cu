@@ -1,0 +1,461 @@
+// Implicit-GEMM convolution on the 5th-gen tensor cores (tcgen05.mma, accumulators in TMEM, operands staged in
+// shared memory by TMA) for sm_100a.  bf16 channels-last activations, fp32 accumulate.
+//
+// Replaces the cuDNN / cuBLAS calls behind nn.Conv2d 3x3 / 1x1 and NIN (models/layers.py:96-118, 537-546) in
+// NCSNpp.forward / DDPM.forward, with the elementwise work around them fused into the epilogue:
+//     out = ((conv(x) + bias[n] + temb[b, n]) + residual) * out_scale
+// (Dense_0 time-embedding bias layerspp.py:263, skip add + 1/sqrt(2) layerspp.py:271-274), and the skip-connection
+// concat (ncsnpp.py:318) folded into the K loop as a second TMA source.
+//
+// GEMM view: M = B*H*W output pixels, N = Cout, K = taps * (C1 + C2).  stride 1, "same" padding.
+//   A tile (128 pixels x 64 channels of ONE filter tap) = one 4-D TMA box {64 c, TW w, TH h, TB b} over the NHWC
+//     activation, started at (c0, w0 + s - pad, h0 + r - pad, b0): the zero padding of the convolution is TMA's
+//     out-of-bounds fill, so there is no im2col buffer and no bounds logic in the kernel.  128B swizzle makes the
+//     box land in the canonical K-major SW128 layout that the UMMA shared-memory descriptor expects.
+//   B tile (BN output channels x 64 k) = a 2-D TMA box over the packed weights [Cout][taps*(C1+C2)].
+//   D tile (128 x BN fp32) lives in TMEM; two accumulator buffers so the epilogue of tile i overlaps the MMAs of
+//     tile i+1.
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected thread),
+// warps 2..5 = epilogue (tcgen05.ld -> bias/temb/residual/scale -> bf16 -> global).  Persistent: grid = min(tiles,
+// 148), static round-robin tile schedule.
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+#include "../../include/b200_sde.h"
+
+namespace b200 {
+
+constexpr int TC_BM = 128;      // pixels per tile (UMMA M)
+constexpr int TC_BK = 64;       // channels per stage (64 bf16 = 128 B = one swizzle row)
+constexpr int TC_THREADS = 192;
+
+struct ConvTcParams {
+  int B, H, W;                  // activation extent (stride 1: output extent too)
+  int C1, C2, Cout;             // Cout = channels of the output tensor (multiple of BN)
+  int taps_w, pad;              // KW (1 or 3) -- KH == KW; pad = KW / 2
+  int TW, TH, TB;               // tile box: TW * TH * TB == 128
+  int tiles_w, tiles_h;         // M tiles per image row / per image column (TB == 1), else 1
+  int num_m, num_n;             // tile counts
+  const float* bias;            // [Cout] or null
+  const float* temb;            // [B][temb_stride] or null
+  int temb_stride;
+  const bf16* res;              // [B, H, W, Cout] or null
+  float out_scale;
+  bf16* out;                    // [B, H, W, Cout]
+};
+
+// ---- PTX wrappers ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
+                                            int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, bf16 inputs, fp32 accumulate; `acc` = 0 overwrites D.
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns: thread t of the warp gets lane (base_lane + t), columns [col, col + 32).
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor, K-major, 128B swizzle: rows of 128 B, 8-row atoms 1024 B apart (SBO = 1024),
+// LBO unused for a K extent of one swizzle atom; version 1 (Blackwell); layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
+         ((uint64_t)2 << 61);
+}
+
+template <int BN>
+struct TcSmem {
+  static constexpr int A_BYTES = TC_BM * TC_BK * 2;            // 16 KB
+  static constexpr int B_BYTES = BN * TC_BK * 2;               // 32 KB (BN = 256)
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;           // barriers + tmem slot, + slack for 1024 B alignment
+};
+
+template <int BN>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
+               const __grid_constant__ CUtensorMap mapW, const ConvTcParams p) {
+  using S = TcSmem<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar0 = base + S::BAR_OFF;
+  // barrier layout (8 B each): full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base slot
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (S::STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * S::STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * S::STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar0 + 8u * (2 * S::STAGES + 4);
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Ctot = p.C1 + p.C2;
+  const int kb_per_tap = Ctot / TC_BK;
+  const int taps = p.taps_w * p.taps_w;
+  const int num_kb = taps * kb_per_tap;
+  const int num_tiles = p.num_m * p.num_n;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA1) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(2 * BN));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  auto tile_coords = [&](int tile, int& mt, int& nt) { nt = tile % p.num_n; mt = tile / p.num_n; };
+  auto m_origin = [&](int mt, int& b0, int& h0, int& w0) {
+    if (p.TB > 1) { b0 = mt * p.TB; h0 = 0; w0 = 0; return; }
+    const int per_img = p.tiles_w * p.tiles_h;
+    b0 = mt / per_img;
+    const int r = mt - b0 * per_img;
+    h0 = (r / p.tiles_w) * p.TH;
+    w0 = (r % p.tiles_w) * p.TW;
+  };
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int mt, nt, b0, h0, w0;
+        tile_coords(tile, mt, nt);
+        m_origin(mt, b0, h0, w0);
+        for (int tap = 0; tap < taps; ++tap) {
+          const int r = tap / p.taps_w, s = tap - r * p.taps_w;
+          for (int kb = 0; kb < kb_per_tap; ++kb) {
+            mbar_wait(empty_bar(stage), phase ^ 1);
+            const uint32_t sa = base + stage * S::STAGE_BYTES, sb = sa + S::A_BYTES;
+            mbar_expect_tx(full_bar(stage), S::STAGE_BYTES);
+            const int c = kb * TC_BK;
+            if (c < p.C1) tma_load_4d(sa, &mapA1, full_bar(stage), c, w0 + s - p.pad, h0 + r - p.pad, b0);
+            else tma_load_4d(sa, &mapA2, full_bar(stage), c - p.C1, w0 + s - p.pad, h0 + r - p.pad, b0);
+            tma_load_2d(sb, &mapW, full_bar(stage), tap * Ctot + c, nt * BN);
+            if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      // instruction descriptor: D = f32, A = B = bf16, both K-major, N = BN, M = 128
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = base + stage * S::STAGE_BYTES, sb = sa + S::A_BYTES;
+          const uint64_t da = make_sw128_desc(sa), db = make_sw128_desc(sb);
+#pragma unroll
+          for (int k = 0; k < TC_BK / 16; ++k) {
+            // advance 16 elements (32 B) along K inside the 128 B swizzle row: +2 in the 16-byte-unit address field
+            tc_mma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          tc_commit(empty_bar(stage));
+          if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(tfull_bar(acc));
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue warps (2..5) =================
+    const int q = warp & 3;                        // TMEM lane quadrant this warp may read
+    const int m_local = q * 32 + lane;
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int mt, nt, b0, h0, w0;
+      tile_coords(tile, mt, nt);
+      m_origin(mt, b0, h0, w0);
+      const int lw = m_local % p.TW, lh = (m_local / p.TW) % p.TH, lb = m_local / (p.TW * p.TH);
+      const int b = b0 + lb, h = h0 + lh, w = w0 + lw;
+      const bool valid = b < p.B;
+      const size_t row = (((size_t)b * p.H + h) * p.W + w) * (size_t)p.Cout + (size_t)nt * BN;
+      const float* tb = (p.temb && valid) ? p.temb + (size_t)b * p.temb_stride + nt * BN : nullptr;
+      const float* bs = p.bias ? p.bias + nt * BN : nullptr;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tc_ld32(t_addr + c0, r);
+        tc_wait_ld();
+        if (valid) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (bs) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 t = __ldg(reinterpret_cast<const float4*>(bs + c0 + j));
+              v[j] += t.x; v[j + 1] += t.y; v[j + 2] += t.z; v[j + 3] += t.w;
+            }
+          }
+          if (tb) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 t = __ldg(reinterpret_cast<const float4*>(tb + c0 + j));
+              v[j] += t.x; v[j + 1] += t.y; v[j + 2] += t.z; v[j + 3] += t.w;
+            }
+          }
+          if (p.res) {
+            const uint4* rp = reinterpret_cast<const uint4*>(p.res + row + c0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 t = __ldg(rp + j);
+              const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&t);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float2 f = __bfloat1622float2(hh[i]);
+                v[j * 8 + 2 * i] += f.x; v[j * 8 + 2 * i + 1] += f.y;
+              }
+            }
+          }
+          uint4* op = reinterpret_cast<uint4*>(p.out + row + c0);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 t;
+            __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              hh[i] = __floats2bfloat162_rn(v[j * 8 + 2 * i] * p.out_scale, v[j * 8 + 2 * i + 1] * p.out_scale);
+            op[j] = t;
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * BN));
+  }
+}
+
+}  // namespace b200
+
+// ---- host side ---------------------------------------------------------------------------------------------------
+using namespace b200;
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  uint64_t v[6];
+  bool operator==(const MapKey& o) const {
+    for (int i = 0; i < 6; ++i) if (v[i] != o.v[i]) return false;
+    return true;
+  }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    uint64_t h = 1469598103934665603ull;
+    for (int i = 0; i < 6; ++i) { h ^= k.v[i]; h *= 1099511628211ull; }
+    return (size_t)h;
+  }
+};
+std::mutex g_map_mu;
+std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;   // descriptors depend only on (pointer, extents, box)
+
+// 4-D map over a channels-last activation [B, H, W, C] (bf16); box {64, TW, TH, TB}, 128B swizzle, zero OOB fill.
+int act_map(CUtensorMap* out, const void* ptr, int B, int H, int W, int C, int TW, int TH, int TB) {
+  MapKey key = {{(uint64_t)ptr, ((uint64_t)B << 32) | (uint32_t)H, ((uint64_t)W << 32) | (uint32_t)C,
+                 ((uint64_t)TW << 32) | (uint32_t)TH, (uint64_t)TB, 4}};
+  {
+    std::lock_guard<std::mutex> g(g_map_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) { *out = it->second; return B200_OK; }
+  }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return B200_ERR_DRIVER;
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {(cuuint32_t)TC_BK, (cuuint32_t)TW, (cuuint32_t)TH, (cuuint32_t)TB};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return B200_ERR_DRIVER;
+  std::lock_guard<std::mutex> g(g_map_mu);
+  g_maps[key] = *out;
+  return B200_OK;
+}
+
+// 2-D map over packed weights [Cout][Ktot] (bf16, K contiguous); box {64, BN}.
+int weight_map(CUtensorMap* out, const void* ptr, int Cout, int Ktot, int BN) {
+  MapKey key = {{(uint64_t)ptr, (uint64_t)Cout, (uint64_t)Ktot, (uint64_t)BN, 0, 2}};
+  {
+    std::lock_guard<std::mutex> g(g_map_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) { *out = it->second; return B200_OK; }
+  }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return B200_ERR_DRIVER;
+  cuuint64_t dims[2] = {(cuuint64_t)Ktot, (cuuint64_t)Cout};
+  cuuint64_t strides[1] = {(cuuint64_t)Ktot * 2};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)BN};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return B200_ERR_DRIVER;
+  std::lock_guard<std::mutex> g(g_map_mu);
+  g_maps[key] = *out;
+  return B200_OK;
+}
+
+bool tile_box(int B, int H, int W, int& TW, int& TH, int& TB, int& tiles_w, int& tiles_h) {
+  if (W >= TC_BM) {
+    if (W % TC_BM) return false;
+    TW = TC_BM; TH = 1; TB = 1; tiles_w = W / TC_BM; tiles_h = H;
+    return true;
+  }
+  if (W <= 0 || TC_BM % W) return false;
+  const int rows = TC_BM / W;
+  TW = W; tiles_w = 1;
+  if (rows <= H) {
+    if (H % rows) return false;
+    TH = rows; TB = 1; tiles_h = H / rows;
+    return true;
+  }
+  if (rows % H) return false;
+  TH = H; TB = rows / H; tiles_h = 1;
+  return TB <= 256;
+}
+
+template <int BN>
+int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const ConvTcParams& p, cudaStream_t st) {
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(conv_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN>::TOTAL);
+  });
+  if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
+  const int tiles = p.num_m * p.num_n;
+  const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
+  conv_tc_kernel<BN><<<grid, TC_THREADS, TcSmem<BN>::TOTAL, st>>>(a1, a2, w, p);
+  B200_RETURN_LAST();
+}
+
+}  // namespace
+
+extern "C" int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride) {
+  int TW, TH, TB, tw, th;
+  if (stride != 1 || (ksize != 1 && ksize != 3)) return 0;
+  if (C1 <= 0 || C1 % TC_BK || C2 < 0 || C2 % TC_BK || Cout <= 0 || Cout % 128) return 0;
+  if (B <= 0 || !tile_box(B, H, W, TW, TH, TB, tw, th)) return 0;
+  return 1;
+}
+
+extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
+                              const float* temb, int temb_stride, const void* res, float out_scale, void* out, int B,
+                              int H, int W, int Cout, int ksize, cudaStream_t st) {
+  if (!x1 || !w || !out || (C2 > 0 && !x2)) return B200_ERR_ARG;
+  if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1)) return B200_ERR_UNSUPPORTED;
+  ConvTcParams p;
+  p.B = B; p.H = H; p.W = W; p.C1 = C1; p.C2 = C2; p.Cout = Cout; p.taps_w = ksize; p.pad = ksize / 2;
+  tile_box(B, H, W, p.TW, p.TH, p.TB, p.tiles_w, p.tiles_h);
+  p.num_m = p.TB > 1 ? (B + p.TB - 1) / p.TB : B * p.tiles_w * p.tiles_h;
+  int BN = (Cout % 256 == 0) ? 256 : 128;
+  if (BN == 256 && p.num_m * (Cout / 256) < B200_NUM_SMS) BN = 128;   // small levels: more, narrower tiles
+  p.num_n = Cout / BN;
+  p.bias = bias; p.temb = temb; p.temb_stride = temb_stride; p.res = (const bf16*)res; p.out_scale = out_scale;
+  p.out = (bf16*)out;
+  const int Ktot = ksize * ksize * (C1 + C2);
+  CUtensorMap a1, a2, wm;
+  int rc = act_map(&a1, x1, B, H, W, C1, p.TW, p.TH, p.TB);
+  if (rc) return rc;
+  if (C2 > 0) { rc = act_map(&a2, x2, B, H, W, C2, p.TW, p.TH, p.TB); if (rc) return rc; }
+  else a2 = a1;
+  rc = weight_map(&wm, w, Cout, Ktot, BN);
+  if (rc) return rc;
+  return BN == 256 ? launch<256>(a1, a2, wm, p, st) : launch<128>(a1, a2, wm, p, st);
+}

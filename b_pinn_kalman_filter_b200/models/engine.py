@@ -416,8 +416,8 @@ class ScoreEngine:
     # ---- kernel selection -------------------------------------------------------------------------------------
     def emit_conv(self, b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, stride, pad, key):
         from . import tc
-        if self.use_tc and tc.conv_supported(x, x2, out, ksize, stride, pad):
-            tc.emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, pad)
+        if self.use_tc and tc.conv_supported(b, x, x2, out, ksize, stride, tuple(pad)):
+            tc.emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, self.conv_flops(b, x, x2, out, ksize))
             self.tc_convs += 1
             return
         self.simt_convs += 1

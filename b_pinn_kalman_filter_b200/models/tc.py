@@ -1,10 +1,25 @@
 """Tensor-core (tcgen05 / TMEM / TMA) launch selection for the score engine.  See csrc/conv_tc.cu."""
+from .. import _lib
+from .._lib import c_float, c_int, c_vp
 
-ENABLED = False
+_lib.register_signature("b200_conv2d_tc_supported", [c_int] * 8)
+_lib.register_signature("b200_conv2d_tc", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_vp,
+                                           c_int, c_int, c_int, c_int, c_int, c_vp])
+
+ENABLED = True
 
 
-def conv_supported(x, x2, out, ksize, stride, pad):
-    return False
+def conv_supported(b, x, x2, out, ksize, stride, pad):
+    if not ENABLED or pad != (ksize // 2, ksize // 2) or (out.H, out.W) != (x.H, x.W):
+        return False
+    c2 = x2.C if x2 is not None else 0
+    return bool(_lib.lib().b200_conv2d_tc_supported(x.C, c2, b.B, x.H, x.W, out.C, ksize, stride))
+
+
+def emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
+    p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+    b.emit("b200_conv2d_tc", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, b.temb_stride, res, out_scale,
+           out, b.B, x.H, x.W, out.C, ksize, flops=flops)
 
 
 def attention_supported(L, C):

@@ -1,0 +1,79 @@
+"""tcgen05 implicit-GEMM convolution (csrc/conv_tc.cu) through the C ABI vs a plain PyTorch fp32 reference of the same
+op on the same bf16-rounded operands.  Tolerance: bf16 output rounding (2^-8 relative) + fp32 accumulation order."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [  # B, H, W, C1, C2, Cout, k
+    (4, 32, 32, 128, 0, 128, 3),
+    (3, 16, 16, 256, 256, 256, 3),
+    (5, 8, 8, 256, 0, 256, 3),       # B not a multiple of the 2-image tile
+    (9, 4, 4, 256, 256, 256, 1),     # 8-image tiles, ragged batch
+    (2, 32, 32, 128, 0, 768, 1),     # fused q,k,v projection: three N tiles
+    (2, 64, 64, 128, 128, 128, 3),   # DDPM 64x64 level, two-row tiles
+    (1, 128, 128, 64, 0, 128, 3),    # one tile per image row
+    (1, 16, 256, 64, 0, 128, 3),     # two tiles per image row
+    (160, 16, 16, 256, 128, 256, 3),  # more tiles than SMs: persistent loop + both TMEM buffers
+]
+
+
+def _run(dev, B, H, W, C1, C2, Cout, k, with_bias=True, with_temb=True, with_res=True, scale=0.70710678):
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import tc  # noqa: F401  registers the signatures
+    g = torch.Generator(device="cpu").manual_seed(B * 1000 + H + C1 + Cout + k)
+    rn = lambda *s: torch.randn(*s, generator=g)
+    x1 = rn(B, H, W, C1).to(dev, torch.bfloat16)
+    x2 = rn(B, H, W, C2).to(dev, torch.bfloat16) if C2 else None
+    Ct = C1 + C2
+    w = (rn(Cout, k, k, Ct) / (k * k * Ct) ** 0.5).to(dev, torch.bfloat16)
+    bias = rn(Cout).to(dev) if with_bias else None
+    temb = rn(B, Cout + 64).to(dev) if with_temb else None   # a column slice of a wider [B, sum(out_ch)] table
+    res = rn(B, H, W, Cout).to(dev, torch.bfloat16) if with_res else None
+    out = torch.full((B, H, W, Cout), float("nan"), device=dev, dtype=torch.bfloat16)
+    lib = _lib.lib()
+    assert lib.b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, k, 1) == 1
+    rc = lib.b200_conv2d_tc(_lib.ptr(x1), C1, _lib.ptr(x2), C2, _lib.ptr(w), _lib.ptr(bias),
+                            (temb.data_ptr() + 4 * 32) if with_temb else None, Cout + 64, _lib.ptr(res), scale,
+                            _lib.ptr(out), B, H, W, Cout, k, _lib.stream())
+    _lib.check(rc, "b200_conv2d_tc")
+    torch.cuda.synchronize()
+    xx = torch.cat([x1, x2], -1) if C2 else x1
+    ref = torch.nn.functional.conv2d(xx.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), padding=k // 2)
+    ref = ref.permute(0, 2, 3, 1)
+    if with_bias:
+        ref = ref + bias
+    if with_temb:
+        ref = ref + temb[:, None, None, 32:32 + Cout]
+    if with_res:
+        ref = ref + res.float()
+    ref = ref * scale
+    return out.float(), ref
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_conv_tc_matches_torch_fp32(cuda, shape):
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    out, ref = _run(cuda, *shape)
+    assert torch.isfinite(out).all()
+    err = (out - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    assert err <= 2 ** -7 * scale, (err, scale)
+    rel = ((out - ref).norm() / ref.norm()).item()
+    assert rel < 4e-3, rel
+
+
+def test_conv_tc_plain_epilogue(cuda):
+    out, ref = _run(cuda, 2, 16, 16, 128, 0, 256, 3, with_bias=False, with_temb=False, with_res=False, scale=1.0)
+    assert ((out - ref).norm() / ref.norm()).item() < 4e-3
+
+
+def test_conv_tc_unsupported_shapes_are_refused(cuda):
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import tc  # noqa: F401
+    lib = _lib.lib()
+    assert lib.b200_conv2d_tc_supported(8, 0, 4, 32, 32, 128, 3, 1) == 0      # Cin = 8 (image stem)
+    assert lib.b200_conv2d_tc_supported(128, 0, 4, 32, 32, 8, 3, 1) == 0      # Cout = 8 (image head)
+    assert lib.b200_conv2d_tc_supported(128, 0, 4, 33, 33, 128, 3, 2) == 0    # stride 2
+    assert lib.b200_conv2d_tc_supported(128, 0, 4, 24, 24, 128, 3, 1) == 0    # 128 % W != 0
