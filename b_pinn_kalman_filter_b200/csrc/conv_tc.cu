@@ -18,12 +18,10 @@
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected thread),
 // warps 2..5 = epilogue (tcgen05.ld -> bias/temb/residual/scale -> bf16 -> global).  Persistent: grid = min(tiles,
 // 148), static round-robin tile schedule.
-#include <cuda.h>
-
 #include <mutex>
 #include <unordered_map>
 
-#include "common.cuh"
+#include "tc_common.cuh"
 #include "../../include/b200_sde.h"
 
 namespace b200 {
@@ -46,73 +44,6 @@ struct ConvTcParams {
   float out_scale;
   bf16* out;                    // [B, H, W, Cout]
 };
-
-// ---- PTX wrappers ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2,
-                                            int c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem]^T, bf16 inputs, fp32 accumulate; `acc` = 0 overwrites D.
-__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                            uint32_t acc) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc) : "memory");
-}
-// 32 lanes x 32 consecutive fp32 columns: thread t of the warp gets lane (base_lane + t), columns [col, col + 32).
-__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t* r) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// Shared-memory matrix descriptor, K-major, 128B swizzle: rows of 128 B, 8-row atoms 1024 B apart (SBO = 1024),
-// LBO unused for a K extent of one swizzle atom; version 1 (Blackwell); layout type 2 = SWIZZLE_128B.
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
-  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
-         ((uint64_t)2 << 61);
-}
 
 template <int BN>
 struct TcSmem {
@@ -329,67 +260,36 @@ EncodeTiledFn get_encode() {
 }
 
 struct MapKey {
-  uint64_t v[6];
+  uint64_t v[14];
   bool operator==(const MapKey& o) const {
-    for (int i = 0; i < 6; ++i) if (v[i] != o.v[i]) return false;
+    for (int i = 0; i < 14; ++i) if (v[i] != o.v[i]) return false;
     return true;
   }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     uint64_t h = 1469598103934665603ull;
-    for (int i = 0; i < 6; ++i) { h ^= k.v[i]; h *= 1099511628211ull; }
+    for (int i = 0; i < 14; ++i) { h ^= k.v[i]; h *= 1099511628211ull; }
     return (size_t)h;
   }
 };
 std::mutex g_map_mu;
-std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;   // descriptors depend only on (pointer, extents, box)
+std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 
-// 4-D map over a channels-last activation [B, H, W, C] (bf16); box {64, TW, TH, TB}, 128B swizzle, zero OOB fill.
+// 4-D map over a channels-last activation [B, H, W, C] (bf16); box {64, TW, TH, TB}.
 int act_map(CUtensorMap* out, const void* ptr, int B, int H, int W, int C, int TW, int TH, int TB) {
-  MapKey key = {{(uint64_t)ptr, ((uint64_t)B << 32) | (uint32_t)H, ((uint64_t)W << 32) | (uint32_t)C,
-                 ((uint64_t)TW << 32) | (uint32_t)TH, (uint64_t)TB, 4}};
-  {
-    std::lock_guard<std::mutex> g(g_map_mu);
-    auto it = g_maps.find(key);
-    if (it != g_maps.end()) { *out = it->second; return B200_OK; }
-  }
-  EncodeTiledFn enc = get_encode();
-  if (!enc) return B200_ERR_DRIVER;
-  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
-  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-  cuuint32_t box[4] = {(cuuint32_t)TC_BK, (cuuint32_t)TW, (cuuint32_t)TH, (cuuint32_t)TB};
-  cuuint32_t es[4] = {1, 1, 1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, es,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return B200_ERR_DRIVER;
-  std::lock_guard<std::mutex> g(g_map_mu);
-  g_maps[key] = *out;
-  return B200_OK;
+  const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+  const uint64_t strides[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
+  const uint32_t box[4] = {(uint32_t)TC_BK, (uint32_t)TW, (uint32_t)TH, (uint32_t)TB};
+  return tc_tensor_map(out, ptr, 4, dims, strides, box, 0);
 }
 
 // 2-D map over packed weights [Cout][Ktot] (bf16, K contiguous); box {64, BN}.
 int weight_map(CUtensorMap* out, const void* ptr, int Cout, int Ktot, int BN) {
-  MapKey key = {{(uint64_t)ptr, (uint64_t)Cout, (uint64_t)Ktot, (uint64_t)BN, 0, 2}};
-  {
-    std::lock_guard<std::mutex> g(g_map_mu);
-    auto it = g_maps.find(key);
-    if (it != g_maps.end()) { *out = it->second; return B200_OK; }
-  }
-  EncodeTiledFn enc = get_encode();
-  if (!enc) return B200_ERR_DRIVER;
-  cuuint64_t dims[2] = {(cuuint64_t)Ktot, (cuuint64_t)Cout};
-  cuuint64_t strides[1] = {(cuuint64_t)Ktot * 2};
-  cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)BN};
-  cuuint32_t es[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, es,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return B200_ERR_DRIVER;
-  std::lock_guard<std::mutex> g(g_map_mu);
-  g_maps[key] = *out;
-  return B200_OK;
+  const uint64_t dims[2] = {(uint64_t)Ktot, (uint64_t)Cout};
+  const uint64_t strides[1] = {(uint64_t)Ktot * 2};
+  const uint32_t box[2] = {(uint32_t)TC_BK, (uint32_t)BN};
+  return tc_tensor_map(out, ptr, 2, dims, strides, box, 1);
 }
 
 bool tile_box(int B, int H, int W, int& TW, int& TH, int& TB, int& tiles_w, int& tiles_h) {
@@ -426,6 +326,36 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
 }
 
 }  // namespace
+
+namespace b200 {
+int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides,
+                  const uint32_t* box, int l2_256) {
+  MapKey key;
+  for (int i = 0; i < 14; ++i) key.v[i] = 0;
+  key.v[0] = (uint64_t)ptr; key.v[1] = (uint64_t)rank | ((uint64_t)l2_256 << 8);
+  for (int i = 0; i < rank; ++i) { key.v[2 + i] = dims[i]; key.v[6 + i] = box[i]; }
+  for (int i = 0; i + 1 < rank; ++i) key.v[10 + i] = strides[i];
+  {
+    std::lock_guard<std::mutex> g(g_map_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) { *out = it->second; return B200_OK; }
+  }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return B200_ERR_DRIVER;
+  cuuint64_t d[4], st[3];
+  cuuint32_t bx[4], es[4] = {1, 1, 1, 1};
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
+  for (int i = 0; i + 1 < rank; ++i) st[i] = strides[i];
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   l2_256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return B200_ERR_DRIVER;
+  std::lock_guard<std::mutex> g(g_map_mu);
+  g_maps[key] = *out;
+  return B200_OK;
+}
+}  // namespace b200
 
 extern "C" int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride) {
   int TW, TH, TB, tw, th;

@@ -6,6 +6,9 @@ _lib.register_signature("b200_conv2d_tc_supported", [c_int] * 8)
 _lib.register_signature("b200_conv2d_tc", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_vp,
                                            c_int, c_int, c_int, c_int, c_int, c_vp])
 
+_lib.register_signature("b200_attention_tc_supported", [c_int, c_int])
+_lib.register_signature("b200_attention_tc", [c_vp, c_vp, c_int, c_int, c_int, c_float, c_vp])
+
 ENABLED = True
 
 
@@ -23,4 +26,8 @@ def emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
 
 
 def attention_supported(L, C):
-    return False
+    return ENABLED and bool(_lib.lib().b200_attention_tc_supported(L, C))
+
+
+def emit_attention(b, qkv, out, L, C):
+    b.emit("b200_attention_tc", qkv, out, b.B, L, C, float(int(C) ** (-0.5)), flops=4 * b.B * L * L * C)

@@ -118,6 +118,11 @@ int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w
 int b200_attention_simt(const void* q, const void* k, const void* v, void* out, int dtype, int B, int L, int C,
                         int ldq, int ldk, int ldv, int ldo, float scale, cudaStream_t stream);
 
+/* the same attention on the tcgen05 tensor cores for L = 256 tokens, C = 256 channels (every shipped network's
+ * attention shape): qkv = fused projection [B, L, 3C] bf16 (q | k | v), out [B, L, C] bf16; scores stay in TMEM. */
+int b200_attention_tc_supported(int L, int C);
+int b200_attention_tc(const void* qkv, void* out, int B, int L, int C, float scale, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

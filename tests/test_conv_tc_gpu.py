@@ -77,3 +77,25 @@ def test_conv_tc_unsupported_shapes_are_refused(cuda):
     assert lib.b200_conv2d_tc_supported(128, 0, 4, 32, 32, 8, 3, 1) == 0      # Cout = 8 (image head)
     assert lib.b200_conv2d_tc_supported(128, 0, 4, 33, 33, 128, 3, 2) == 0    # stride 2
     assert lib.b200_conv2d_tc_supported(128, 0, 4, 24, 24, 128, 3, 1) == 0    # 128 % W != 0
+
+
+@pytest.mark.parametrize("B", [1, 3, 150])
+def test_attention_tc_matches_torch_fp32(cuda, B):
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import tc  # noqa: F401
+    L, C = 256, 256
+    g = torch.Generator(device="cpu").manual_seed(B)
+    qkv = torch.randn(B, L, 3 * C, generator=g)
+    qkv[:, :, :C] *= 2.0          # sharper softmax rows
+    qkv = qkv.to(cuda, torch.bfloat16)
+    out = torch.full((B, L, C), float("nan"), device=cuda, dtype=torch.bfloat16)
+    lib = _lib.lib()
+    assert lib.b200_attention_tc_supported(L, C) == 1 and lib.b200_attention_tc_supported(64, 64) == 0
+    _lib.check(lib.b200_attention_tc(_lib.ptr(qkv), _lib.ptr(out), B, L, C, C ** -0.5, _lib.stream()), "attention_tc")
+    torch.cuda.synchronize()
+    q, k, v = (t.float() for t in qkv.split(C, dim=-1))
+    ref = torch.softmax(q @ k.transpose(1, 2) * C ** -0.5, dim=-1) @ v
+    assert torch.isfinite(out).all()
+    rel = ((out.float() - ref).norm() / ref.norm()).item()
+    assert rel < 8e-3, rel          # P and the output are rounded to bf16 (2^-9 relative each)
+    assert (out.float() - ref).abs().max().item() < 2e-2 * ref.abs().max().item()
