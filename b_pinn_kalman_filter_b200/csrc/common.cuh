@@ -32,6 +32,11 @@ template <> __device__ __forceinline__ float from_f<float>(float v) { return v; 
 template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __float2bfloat16_rn(v); }
 
 __device__ __forceinline__ float silu(float v) { return v / (1.0f + __expf(-v)); }
+// bf16 paths: MUFU.EX2 + MUFU.RCP (2 ulp) instead of the IEEE division -- the result is rounded to 8 bits anyway
+__device__ __forceinline__ float silu_fast(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
+template <typename T> __device__ __forceinline__ float silu_t(float v);
+template <> __device__ __forceinline__ float silu_t<float>(float v) { return silu(v); }
+template <> __device__ __forceinline__ float silu_t<__nv_bfloat16>(float v) { return silu_fast(v); }
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

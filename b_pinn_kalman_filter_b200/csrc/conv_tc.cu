@@ -42,7 +42,10 @@ struct ConvTcParams {
   int temb_stride;
   const bf16* res;              // [B, H, W, Cout] or null
   float out_scale;
-  bf16* out;                    // [B, H, W, Cout]
+  bf16* out;                    // [B, H, W, Cout]                        (EPI 0)
+  float* out_nchw;              // [B, cout_true, H, W] fp32, * sample_mul[b]  (EPI 1: network head, ncsnpp.py:371-379)
+  const float* sample_mul;
+  int cout_true;
 };
 
 template <int BN>
@@ -50,12 +53,13 @@ struct TcSmem {
   static constexpr int A_BYTES = TC_BM * TC_BK * 2;            // 16 KB
   static constexpr int B_BYTES = BN * TC_BK * 2;               // 32 KB (BN = 256)
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : 6;
+  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;
   static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;           // barriers + tmem slot, + slack for 1024 B alignment
 };
 
-template <int BN>
+template <int BN, int EPI>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapW, const ConvTcParams p) {
@@ -86,7 +90,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
   }
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(2 * BN));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(S::TMEM_COLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   tc_fence_before();
@@ -173,6 +177,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
+      if constexpr (EPI == 1) {
+        uint32_t r[16];
+        tc_ld16(t_addr, r);
+        tc_wait_ld();
+        if (valid) {
+          const float mul = (p.sample_mul ? __ldg(p.sample_mul + b) : 1.0f) * p.out_scale;
+          float* op = p.out_nchw + (((size_t)b * p.cout_true) * p.H + h) * p.W + w;
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (j < p.cout_true)
+              op[(size_t)j * p.H * p.W] = (__uint_as_float(r[j]) + (bs ? __ldg(bs + j) : 0.0f)) * mul;
+        }
+      } else {
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 32) {
         uint32_t r[32];
@@ -221,6 +238,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           }
         }
       }
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(acc));
@@ -231,7 +249,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(2 * BN));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(S::TMEM_COLS));
   }
 }
 
@@ -311,17 +329,17 @@ bool tile_box(int B, int H, int W, int& TW, int& TH, int& TB, int& tiles_w, int&
   return TB <= 256;
 }
 
-template <int BN>
+template <int BN, int EPI>
 int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const ConvTcParams& p, cudaStream_t st) {
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN>::TOTAL);
+    attr_err = cudaFuncSetAttribute(conv_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN>::TOTAL);
   });
   if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
-  conv_tc_kernel<BN><<<grid, TC_THREADS, TcSmem<BN>::TOTAL, st>>>(a1, a2, w, p);
+  conv_tc_kernel<BN, EPI><<<grid, TC_THREADS, TcSmem<BN>::TOTAL, st>>>(a1, a2, w, p);
   B200_RETURN_LAST();
 }
 
@@ -357,35 +375,40 @@ int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* d
 }
 }  // namespace b200
 
-extern "C" int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride) {
+extern "C" int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride,
+                                        int out_mode) {
   int TW, TH, TB, tw, th;
   if (stride != 1 || (ksize != 1 && ksize != 3)) return 0;
-  if (C1 <= 0 || C1 % TC_BK || C2 < 0 || C2 % TC_BK || Cout <= 0 || Cout % 128) return 0;
+  if (C1 <= 0 || C1 % TC_BK || C2 < 0 || C2 % TC_BK || Cout <= 0) return 0;
+  if (out_mode == 0 ? (Cout % 128 != 0) : (out_mode != 1 || Cout > 16)) return 0;
   if (B <= 0 || !tile_box(B, H, W, TW, TH, TB, tw, th)) return 0;
   return 1;
 }
 
 extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
-                              const float* temb, int temb_stride, const void* res, float out_scale, void* out, int B,
-                              int H, int W, int Cout, int ksize, cudaStream_t st) {
+                              const float* temb, int temb_stride, const void* res, float out_scale, void* out,
+                              int out_mode, const float* sample_mul, int B, int H, int W, int Cout, int ksize,
+                              cudaStream_t st) {
   if (!x1 || !w || !out || (C2 > 0 && !x2)) return B200_ERR_ARG;
-  if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1)) return B200_ERR_UNSUPPORTED;
+  if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1, out_mode)) return B200_ERR_UNSUPPORTED;
+  if (out_mode == 1 && (temb || res)) return B200_ERR_UNSUPPORTED;
   ConvTcParams p;
   p.B = B; p.H = H; p.W = W; p.C1 = C1; p.C2 = C2; p.Cout = Cout; p.taps_w = ksize; p.pad = ksize / 2;
   tile_box(B, H, W, p.TW, p.TH, p.TB, p.tiles_w, p.tiles_h);
   p.num_m = p.TB > 1 ? (B + p.TB - 1) / p.TB : B * p.tiles_w * p.tiles_h;
-  int BN = (Cout % 256 == 0) ? 256 : 128;
+  int BN = out_mode == 1 ? 16 : ((Cout % 256 == 0) ? 256 : 128);
   if (BN == 256 && p.num_m * (Cout / 256) < B200_NUM_SMS) BN = 128;   // small levels: more, narrower tiles
-  p.num_n = Cout / BN;
+  p.num_n = out_mode == 1 ? 1 : Cout / BN;
   p.bias = bias; p.temb = temb; p.temb_stride = temb_stride; p.res = (const bf16*)res; p.out_scale = out_scale;
-  p.out = (bf16*)out;
+  p.out = (bf16*)out; p.out_nchw = (float*)out; p.sample_mul = sample_mul; p.cout_true = Cout;
   const int Ktot = ksize * ksize * (C1 + C2);
   CUtensorMap a1, a2, wm;
   int rc = act_map(&a1, x1, B, H, W, C1, p.TW, p.TH, p.TB);
   if (rc) return rc;
   if (C2 > 0) { rc = act_map(&a2, x2, B, H, W, C2, p.TW, p.TH, p.TB); if (rc) return rc; }
   else a2 = a1;
-  rc = weight_map(&wm, w, Cout, Ktot, BN);
+  rc = weight_map(&wm, w, Cout, Ktot, BN);          // rows beyond Cout are zero-filled by TMA (head: 3 of 16)
   if (rc) return rc;
-  return BN == 256 ? launch<256>(a1, a2, wm, p, st) : launch<128>(a1, a2, wm, p, st);
+  if (out_mode == 1) return launch<16, 1>(a1, a2, wm, p, st);
+  return BN == 256 ? launch<256, 0>(a1, a2, wm, p, st) : launch<128, 0>(a1, a2, wm, p, st);
 }

@@ -99,6 +99,55 @@ __global__ void __launch_bounds__(256) linear_kernel(const float* __restrict__ x
   }
 }
 
+// Tiled fp32 GEMM for the same op when the batch is large: 64 samples x 64 outputs per block, K in chunks of 16,
+// 4x4 outputs per thread.  (The per-sample kernel above re-reads W once per sample.)
+__global__ void __launch_bounds__(256) linear_tiled_kernel(const float* __restrict__ x, const float* __restrict__ W,
+                                                           const float* __restrict__ bias, float* __restrict__ out,
+                                                           int B, int K, int N, int act_in, int act_out) {
+  __shared__ __align__(16) float As[16][64 + 4];
+  __shared__ __align__(16) float Bs[16][64 + 4];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int b0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  const int lr = tid >> 2, lk = (tid & 3) * 4;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int k0 = 0; k0 < K; k0 += 16) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), w = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (b0 + lr < B) a = __ldg(reinterpret_cast<const float4*>(x + (size_t)(b0 + lr) * K + k0 + lk));
+    if (n0 + lr < N) w = __ldg(reinterpret_cast<const float4*>(W + (size_t)(n0 + lr) * K + k0 + lk));
+    if (act_in) { a.x = silu(a.x); a.y = silu(a.y); a.z = silu(a.z); a.w = silu(a.w); }
+    __syncthreads();
+    As[lk][lr] = a.x; As[lk + 1][lr] = a.y; As[lk + 2][lr] = a.z; As[lk + 3][lr] = a.w;
+    Bs[lk][lr] = w.x; Bs[lk + 1][lr] = w.y; Bs[lk + 2][lr] = w.z; Bs[lk + 3][lr] = w.w;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const float4 av = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 bv = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+      const float aa[4] = {av.x, av.y, av.z, av.w}, bb[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(aa[i], bb[j], acc[i][j]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int b = b0 + ty * 4 + i;
+    if (b >= B) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= N) continue;
+      float v = acc[i][j] + (bias ? bias[n] : 0.0f);
+      out[(size_t)b * N + n] = act_out ? silu(v) : v;
+    }
+  }
+}
+
 // out = (a + b) * s    (8-wide)
 template <typename T>
 __global__ void add_scale_kernel(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ out, long long nvec,
@@ -181,6 +230,11 @@ extern "C" int b200_linear_f32(const float* x, const float* W, const float* bias
                                int act_in, int act_out, cudaStream_t st) {
   if (!x || !W || !out || B < 0 || K <= 0 || N <= 0 || K > 8192) return B200_ERR_ARG;
   if (B == 0) return B200_OK;
+  if (B >= 16 && K % 16 == 0) {
+    dim3 grid((N + 63) / 64, (B + 63) / 64);
+    linear_tiled_kernel<<<grid, 256, 0, st>>>(x, W, bias, out, B, K, N, act_in, act_out);
+    B200_RETURN_LAST();
+  }
   int gx = (N + 7) / 8;
   if (gx > 64) gx = 64;
   dim3 grid(gx, B);

@@ -37,7 +37,17 @@ __global__ void __launch_bounds__(256) gn_partial_kernel(GnArgs a) {
   float s[8], q[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { s[j] = 0.f; q[j] = 0.f; }
-  for (int p = p_begin + pl; p < p_end; p += ppt) {
+  int p = p_begin + pl;
+  for (; p + 3 * ppt < p_end; p += 4 * ppt) {     // 4 independent 16/32-byte loads in flight per thread
+    float v[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) Vec8<T>::load(src + (size_t)(p + u * ppt) * cs, v[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s[j] += v[u][j]; q[j] = fmaf(v[u][j], v[u][j], q[j]); }
+  }
+  for (; p < p_end; p += ppt) {
     float v[8];
     Vec8<T>::load(src + (size_t)p * cs, v);
 #pragma unroll
@@ -98,13 +108,28 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(GnArgs a) {
   if (c0 < a.C1) { src = (const T*)a.x1; cs = a.C1; cc = c0; } else { src = (const T*)a.x2; cs = a.C2; cc = c0 - a.C1; }
   src += (size_t)b * a.HW * cs + cc;
   T* dst = (T*)a.out + (size_t)b * a.HW * C + c0;
-  for (int p = p_begin + pl; p < p_end; p += ppt) {
+  int p = p_begin + pl;
+  for (; p + 3 * ppt < p_end; p += 4 * ppt) {
+    float v[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) Vec8<T>::load(src + (size_t)(p + u * ppt) * cs, v[u]);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float y = fmaf(v[u][j], sc[j], sf[j]);
+        v[u][j] = a.act ? silu_t<T>(y) : y;
+      }
+      Vec8<T>::store(dst + (size_t)(p + u * ppt) * C, v[u]);
+    }
+  }
+  for (; p < p_end; p += ppt) {
     float v[8];
     Vec8<T>::load(src + (size_t)p * cs, v);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float y = fmaf(v[j], sc[j], sf[j]);
-      v[j] = a.act ? silu(y) : y;
+      v[j] = a.act ? silu_t<T>(y) : y;
     }
     Vec8<T>::store(dst + (size_t)p * C, v);
   }
@@ -122,7 +147,7 @@ using namespace b200;
 
 extern "C" int b200_gn_nsplit(int B, int HW) {
   // enough blocks to fill 148 SMs a few times over, but never fewer than 64 pixels per block
-  int want = (B200_NUM_SMS * 4 + B - 1) / (B > 0 ? B : 1);
+  int want = (B200_NUM_SMS * 8 + B - 1) / (B > 0 ? B : 1);
   int maxs = HW / 64 > 0 ? HW / 64 : 1;
   int s = want < maxs ? want : maxs;
   if (s < 1) s = 1;

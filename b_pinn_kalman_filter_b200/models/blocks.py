@@ -89,6 +89,7 @@ class Net:
         """NCHW fp32 -> channels-last (8-wide, zero padded), with `2x - 1` folded in (ncsnpp.py:259-261)."""
         b = self.b
         x = b.new(H, W, 8, channels)
+        self.x_stem = x
         if b.dry:
             return x
         plan = b.plan
@@ -96,6 +97,13 @@ class Net:
         plan.out = torch.zeros(b.B, channels, H, W, device=b.e.device, dtype=torch.float32)
         b.emit("b200_nchw_to_nhwc", plan.x_in.data_ptr(), x, b.dt, b.B, channels, H, W, 8,
                2.0 if rescale else 1.0, -1.0 if rescale else 0.0)
+        if b.e.use_tc:
+            # tensor-core stem: the same image in a 64-channel (one 128-byte TMA row) zero-padded tensor
+            self.x_stem = b.new(H, W, 64, channels)
+            b.emit("b200_nchw_to_nhwc", plan.x_in.data_ptr(), self.x_stem, b.dt, b.B, channels, H, W, 64,
+                   2.0 if rescale else 1.0, -1.0 if rescale else 0.0)
+        else:
+            self.x_stem = x
         return x
 
     def output_conv3x3(self, a, idx, channels, init_scale):

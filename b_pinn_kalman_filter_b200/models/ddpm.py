@@ -31,7 +31,7 @@ def build_ddpm(b, config):
         # ResnetBlockDDPM: 32 groups, Conv_1 init_scale 0, NIN shortcut, no 1/sqrt(2)
         return net.resblock_ddpmpp(net.next_module(), x, x2, out_ch, skip_rescale=False, init_scale=0., groups=32)
 
-    hs = [net.conv3x3(x, net.next_module(), nf)]
+    hs = [net.conv3x3(net.x_stem, net.next_module(), nf)]
     for lvl in range(levels):
         for _ in range(nres):
             h = resblock(hs[-1], nf * ch_mult[lvl])

@@ -249,6 +249,15 @@ class Builder:
             temb_ptr = self.temb_all.data_ptr() + 4 * temb_off
         p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
         if nchw_out is not None:
+            from . import tc
+            fl = 2 * self.B * Ho * Wo * cout * cin_true * ksize * ksize
+            mul_ptr = self.sample_mul.data_ptr() if self.sample_mul is not None else None
+            if (self.e.use_tc and x2 is None and temb_off is None and res is None and stride == 1
+                    and tuple(pad) == (ksize // 2, ksize // 2) and tc.head_supported(self, x, cout, ksize)):
+                tc.emit_head(self, x, w, bias, out_scale, nchw_out.data_ptr(), mul_ptr, cout, ksize, fl)
+                self.e.tc_convs += 1
+                return None
+            self.e.simt_convs += 1
             self.emit("b200_conv2d_simt", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, self.temb_stride,
                       res, out_scale, nchw_out.data_ptr(), 1,
                       self.sample_mul.data_ptr() if self.sample_mul is not None else None, self.dt, self.B, x.H, x.W,

@@ -49,7 +49,7 @@ def build_ncsnpp(b, config):
     x = net.input_image(channels, size, size, rescale=not config.data.centered)
     pyramid_in = x if progressive_input != "none" else None
 
-    hs = [net.conv3x3(x, net.next_module(), nf)]
+    hs = [net.conv3x3(net.x_stem, net.next_module(), nf)]
     hs_c = [nf]
     in_ch = nf
 

@@ -2,9 +2,9 @@
 from .. import _lib
 from .._lib import c_float, c_int, c_vp
 
-_lib.register_signature("b200_conv2d_tc_supported", [c_int] * 8)
+_lib.register_signature("b200_conv2d_tc_supported", [c_int] * 9)
 _lib.register_signature("b200_conv2d_tc", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_vp,
-                                           c_int, c_int, c_int, c_int, c_int, c_vp])
+                                           c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp])
 
 _lib.register_signature("b200_attention_tc_supported", [c_int, c_int])
 _lib.register_signature("b200_attention_tc", [c_vp, c_vp, c_int, c_int, c_int, c_float, c_vp])
@@ -16,13 +16,23 @@ def conv_supported(b, x, x2, out, ksize, stride, pad):
     if not ENABLED or pad != (ksize // 2, ksize // 2) or (out.H, out.W) != (x.H, x.W):
         return False
     c2 = x2.C if x2 is not None else 0
-    return bool(_lib.lib().b200_conv2d_tc_supported(x.C, c2, b.B, x.H, x.W, out.C, ksize, stride))
+    return bool(_lib.lib().b200_conv2d_tc_supported(x.C, c2, b.B, x.H, x.W, out.C, ksize, stride, 0))
 
 
 def emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
     p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
     b.emit("b200_conv2d_tc", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, b.temb_stride, res, out_scale,
-           out, b.B, x.H, x.W, out.C, ksize, flops=flops)
+           out, 0, None, b.B, x.H, x.W, out.C, ksize, flops=flops)
+
+
+def head_supported(b, x, cout, ksize):
+    """Network head: conv -> NCHW fp32 * sample_mul (Cout <= 16 on one N = 16 tile)."""
+    return ENABLED and bool(_lib.lib().b200_conv2d_tc_supported(x.C, 0, b.B, x.H, x.W, cout, ksize, 1, 1))
+
+
+def emit_head(b, x, w, bias, out_scale, out_ptr, sample_mul_ptr, cout, ksize, flops):
+    b.emit("b200_conv2d_tc", x, x.C, None, 0, w.data_ptr(), bias.data_ptr(), None, 0, None, out_scale, out_ptr, 1,
+           sample_mul_ptr, b.B, x.H, x.W, cout, ksize, flops=flops)
 
 
 def attention_supported(L, C):

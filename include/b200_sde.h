@@ -109,11 +109,13 @@ int b200_conv2d_simt(const void* x1, int C1, const void* x2, int C2, const void*
                      int stride, int pad_t, int pad_l, cudaStream_t stream);
 /* the same convolution on the tcgen05 tensor cores (bf16 channels-last, stride 1, "same" padding, ksize 1 or 3,
  * C1 % 64 == C2 % 64 == 0, Cout % 128 == 0): TMA-fed implicit GEMM with TMEM accumulators, same fused epilogue.
- * w: packed [Cout][ksize*ksize*(C1+C2)] bf16.  b200_conv2d_tc_supported returns 1 when the shape is taken. */
-int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride);
+ * w: packed [Cout][ksize*ksize*(C1+C2)] bf16.  b200_conv2d_tc_supported returns 1 when the shape is taken.
+ * out_mode 0: channels-last bf16 [B,H,W,Cout].  out_mode 1 (network head, Cout <= 16): NCHW fp32 [B,Cout,H,W] scaled
+ * by sample_mul[b] (`h / used_sigmas`, models/ncsnpp.py:377-379); w then has Cout rows. */
+int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride, int out_mode);
 int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias, const float* temb,
-                   int temb_stride, const void* res, float out_scale, void* out, int B, int H, int W, int Cout,
-                   int ksize, cudaStream_t stream);
+                   int temb_stride, const void* res, float out_scale, void* out, int out_mode, const float* sample_mul,
+                   int B, int H, int W, int Cout, int ksize, cudaStream_t stream);
 /* softmax(q k^T scale) v per image on CUDA cores (models/layerspp.py:82-86); ld* = row strides in elements */
 int b200_attention_simt(const void* q, const void* k, const void* v, void* out, int dtype, int B, int L, int C,
                         int ldq, int ldk, int ldv, int ldo, float scale, cudaStream_t stream);

@@ -32,10 +32,10 @@ def _run(dev, B, H, W, C1, C2, Cout, k, with_bias=True, with_temb=True, with_res
     res = rn(B, H, W, Cout).to(dev, torch.bfloat16) if with_res else None
     out = torch.full((B, H, W, Cout), float("nan"), device=dev, dtype=torch.bfloat16)
     lib = _lib.lib()
-    assert lib.b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, k, 1) == 1
+    assert lib.b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, k, 1, 0) == 1
     rc = lib.b200_conv2d_tc(_lib.ptr(x1), C1, _lib.ptr(x2), C2, _lib.ptr(w), _lib.ptr(bias),
                             (temb.data_ptr() + 4 * 32) if with_temb else None, Cout + 64, _lib.ptr(res), scale,
-                            _lib.ptr(out), B, H, W, Cout, k, _lib.stream())
+                            _lib.ptr(out), 0, None, B, H, W, Cout, k, _lib.stream())
     _lib.check(rc, "b200_conv2d_tc")
     torch.cuda.synchronize()
     xx = torch.cat([x1, x2], -1) if C2 else x1
@@ -73,10 +73,10 @@ def test_conv_tc_unsupported_shapes_are_refused(cuda):
     from b_pinn_kalman_filter_b200 import _lib
     from b_pinn_kalman_filter_b200.models import tc  # noqa: F401
     lib = _lib.lib()
-    assert lib.b200_conv2d_tc_supported(8, 0, 4, 32, 32, 128, 3, 1) == 0      # Cin = 8 (image stem)
-    assert lib.b200_conv2d_tc_supported(128, 0, 4, 32, 32, 8, 3, 1) == 0      # Cout = 8 (image head)
-    assert lib.b200_conv2d_tc_supported(128, 0, 4, 33, 33, 128, 3, 2) == 0    # stride 2
-    assert lib.b200_conv2d_tc_supported(128, 0, 4, 24, 24, 128, 3, 1) == 0    # 128 % W != 0
+    assert lib.b200_conv2d_tc_supported(8, 0, 4, 32, 32, 128, 3, 1, 0) == 0      # Cin = 8 (image stem)
+    assert lib.b200_conv2d_tc_supported(128, 0, 4, 32, 32, 8, 3, 1, 0) == 0      # Cout = 8 (image head)
+    assert lib.b200_conv2d_tc_supported(128, 0, 4, 33, 33, 128, 3, 2, 0) == 0    # stride 2
+    assert lib.b200_conv2d_tc_supported(128, 0, 4, 24, 24, 128, 3, 1, 0) == 0    # 128 % W != 0
 
 
 @pytest.mark.parametrize("B", [1, 3, 150])
@@ -99,3 +99,24 @@ def test_attention_tc_matches_torch_fp32(cuda, B):
     rel = ((out.float() - ref).norm() / ref.norm()).item()
     assert rel < 8e-3, rel          # P and the output are rounded to bf16 (2^-9 relative each)
     assert (out.float() - ref).abs().max().item() < 2e-2 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("B,H,C,Cout,k", [(3, 32, 128, 3, 3), (2, 64, 128, 1, 3), (5, 8, 256, 3, 1)])
+def test_conv_tc_head_nchw(cuda, B, H, C, Cout, k):
+    """Network head: conv -> NCHW fp32 scaled per sample (out_mode 1)."""
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import tc  # noqa: F401
+    g = torch.Generator(device="cpu").manual_seed(B + C)
+    x = torch.randn(B, H, H, C, generator=g).to(cuda, torch.bfloat16)
+    w = (torch.randn(Cout, k, k, C, generator=g) / (k * k * C) ** 0.5).to(cuda, torch.bfloat16)
+    bias = torch.randn(Cout, generator=g).to(cuda)
+    mul = (torch.rand(B, generator=g) + 0.5).to(cuda)
+    out = torch.full((B, Cout, H, H), float("nan"), device=cuda)
+    lib = _lib.lib()
+    assert lib.b200_conv2d_tc_supported(C, 0, B, H, H, Cout, k, 1, 1) == 1
+    _lib.check(lib.b200_conv2d_tc(_lib.ptr(x), C, None, 0, _lib.ptr(w), _lib.ptr(bias), None, 0, None, 1.0, _lib.ptr(out),
+                                  1, _lib.ptr(mul), B, H, H, Cout, k, _lib.stream()), "conv2d_tc head")
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), bias, padding=k // 2)
+    ref = ref * mul[:, None, None, None]
+    assert (out - ref).abs().max().item() <= 1e-4 * max(1.0, ref.abs().max().item())
