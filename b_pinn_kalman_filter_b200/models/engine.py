@@ -97,12 +97,13 @@ class Plan:
         self.labels = None     # fp32 [B]
         self.out = None        # fp32 NCHW output
         self.launches = 0
+        self.tags = []         # per launch: shape tag (profiling aid)
         self.meta = []         # per launch: (entry point, algorithmic FLOPs) -- what bench.py's roofline is computed from
 
     def flops(self, prefix=None):
         return sum(f for n, f in self.meta if prefix is None or n.startswith(prefix))
 
-    def run_timed(self, stream_ptr):
+    def run_timed(self, stream_ptr, by_tag=False):
         """Runs the plan with a CUDA-event pair around every launch (on the launching stream); returns
         {entry point: (launches, total ms, total FLOPs)}.  Measurement aid for bench.py, not used while sampling."""
         evs = []
@@ -117,7 +118,9 @@ class Plan:
             evs.append((e0, e1))
         stream.synchronize()
         out = {}
-        for (e0, e1), (name, fl) in zip(evs, self.meta):
+        for (e0, e1), (name, fl), tag in zip(evs, self.meta, self.tags):
+            if by_tag:
+                name = name + " " + tag
             n, ms, f = out.get(name, (0, 0.0, 0))
             out[name] = (n + 1, ms + e0.elapsed_time(e1), f + fl)
         return out
@@ -197,10 +200,11 @@ class Builder:
         self.plan.keep.append(t)
         return t
 
-    def emit(self, name, *args, flops=0):
+    def emit(self, name, *args, flops=0, tag=""):
         fn = getattr(self.lib, name)
         self.plan.ops.append((fn, args, name))
         self.plan.meta.append((name, int(flops)))
+        self.plan.tags.append(tag)
 
     # ---- primitives -------------------------------------------------------------------------------------------
     def gn(self, x, key, groups, act, x2=None):

@@ -22,7 +22,8 @@ def conv_supported(b, x, x2, out, ksize, stride, pad):
 def emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
     p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
     b.emit("b200_conv2d_tc", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, b.temb_stride, res, out_scale,
-           out, 0, None, b.B, x.H, x.W, out.C, ksize, flops=flops)
+           out, 0, None, b.B, x.H, x.W, out.C, ksize, flops=flops,
+           tag="%dx%d %dx%d %d->%d" % (ksize, ksize, x.H, x.W, x.C + c2, out.C))
 
 
 def head_supported(b, x, cout, ksize):
