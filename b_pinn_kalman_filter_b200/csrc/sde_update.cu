@@ -13,12 +13,17 @@
 
 namespace b200 {
 
+// With a device step counter the Philox stream id of an update is offset + step * 16, so that a captured CUDA graph
+// (whose kernel arguments are frozen) still draws fresh noise every PC step.  16 >= n_steps + 1 updates per step.
+#define B200_OFFSETS_PER_STEP 16
+
 // ---- per-sample sum of squares of s, and of z (given or generated) : one block per sample -----------------------
 __global__ void __launch_bounds__(256) sumsq_kernel(float* __restrict__ ss_s, float* __restrict__ ss_z,
                                                     const float* __restrict__ s, const float* __restrict__ z,
                                                     long long n_per, uint64_t seed, uint64_t offset,
-                                                    long long elem_base) {
+                                                    long long elem_base, const int* __restrict__ step) {
   __shared__ float red[32];
+  if (step) offset += (uint64_t)(*step) * B200_OFFSETS_PER_STEP;   // graph replay: noise stream follows the device step
   const long long b = blockIdx.x;
   const float* sp = s ? s + b * n_per : nullptr;
   const float* zp = z ? z + b * n_per : nullptr;
@@ -92,11 +97,12 @@ __global__ void __launch_bounds__(256) sde_update_kernel(UpdArgs A) {
       const long long b = e / A.n_per;
       float a, bb, c;
       upd_coefs(A, b, a, bb, c);
+      const uint64_t off = A.offset + (A.step ? (uint64_t)(*A.step) * B200_OFFSETS_PER_STEP : 0);
       float4 xv = reinterpret_cast<const float4*>(A.x)[v];
       float4 sv = __ldcs(reinterpret_cast<const float4*>(A.s) + v);
       float4 zv;
       if (A.z) zv = __ldcs(reinterpret_cast<const float4*>(A.z) + v);
-      else if (c != 0.0f) zv = Philox::normal4(A.seed, A.offset, (uint64_t)((A.elem_base + e) >> 2));
+      else if (c != 0.0f) zv = Philox::normal4(A.seed, off, (uint64_t)((A.elem_base + e) >> 2));
       else zv = make_float4(0.f, 0.f, 0.f, 0.f);
       float4 m;
       m.x = a * xv.x + bb * sv.x; m.y = a * xv.y + bb * sv.y; m.z = a * xv.z + bb * sv.z; m.w = a * xv.w + bb * sv.w;
@@ -114,7 +120,8 @@ __global__ void __launch_bounds__(256) sde_update_kernel(UpdArgs A) {
       if (A.z) zz = A.z[e];
       else if (c != 0.0f) {
         long long ge = A.elem_base + e;
-        float4 q4 = Philox::normal4(A.seed, A.offset, (uint64_t)(ge >> 2));
+        const uint64_t off = A.offset + (A.step ? (uint64_t)(*A.step) * B200_OFFSETS_PER_STEP : 0);
+        float4 q4 = Philox::normal4(A.seed, off, (uint64_t)(ge >> 2));
         zz = ((ge & 3) == 0) ? q4.x : ((ge & 3) == 1) ? q4.y : ((ge & 3) == 2) ? q4.z : q4.w;
       }
       float m = a * A.x[e] + bb * A.s[e];
@@ -143,11 +150,12 @@ __global__ void step_advance_kernel(int* step, int delta) { if (threadIdx.x == 0
 using namespace b200;
 
 extern "C" int b200_sample_sumsq(float* ss_s, float* ss_z, const float* s, const float* z, int B, long long n_per,
-                                 uint64_t seed, uint64_t offset, long long elem_base, cudaStream_t st) {
+                                 uint64_t seed, uint64_t offset, long long elem_base, const int* step,
+                                 cudaStream_t st) {
   if (B < 0 || n_per <= 0 || (!ss_s && !ss_z) || (ss_s && !s)) return B200_ERR_ARG;
   if (B == 0) return B200_OK;
   if ((elem_base & 3) != 0 || (z == nullptr && ss_z && (n_per & 3) != 0 && false)) return B200_ERR_ARG;
-  sumsq_kernel<<<B, 256, 0, st>>>(ss_s, ss_z, s, z, n_per, seed, offset, elem_base);
+  sumsq_kernel<<<B, 256, 0, st>>>(ss_s, ss_z, s, z, n_per, seed, offset, elem_base, step);
   B200_RETURN_LAST();
 }
 

@@ -292,7 +292,7 @@ def langevin_update(x, grad, alpha, snr, z=None, process_group=None):
     with torch.cuda.device(dev):
         st = _lib.stream()
         _lib.check(lib.b200_sample_sumsq(_lib.ptr(ss[0]), _lib.ptr(ss[1]), _lib.ptr(g), _lib.ptr(z), B, n_per, seed, off,
-                                         0, st), "b200_sample_sumsq")
+                                         0, None, st), "b200_sample_sumsq")
         _lib.check(lib.b200_langevin_norm_sums(_lib.ptr(sums), _lib.ptr(ss[0]), _lib.ptr(ss[1]), B, st),
                    "b200_langevin_norm_sums")
         if process_group is not None:
@@ -442,7 +442,7 @@ class FusedPCLoop:
         self.scaled = torch.zeros_like(self.x) if (self.corr and self.corr[0] == "langevin" and
                                                    not bool((mult == 1).all())) else None
         self.graph = None
-        self.offset = 0
+        self.offset_base = 0
         self.launches_per_step = 0
         self.forwards_per_step = (n_steps if self.corr else 0) + (1 if self.pred else 0)
 
@@ -466,7 +466,8 @@ class FusedPCLoop:
                 torch.mul(self.score, self.mult[self.step_host].item(), out=self.scaled)
                 score = self.scaled
             _lib.check(lib.b200_sample_sumsq(_lib.ptr(self.ss[0]), _lib.ptr(self.ss[1]), _lib.ptr(score), zp, B, n_per,
-                                             self.seed, off, self.elem_base, st), "b200_sample_sumsq")
+                                             self.seed, off, self.elem_base, _lib.ptr(self.step_dev), st),
+                       "b200_sample_sumsq")
             _lib.check(lib.b200_langevin_norm_sums(_lib.ptr(self.sums), _lib.ptr(self.ss[0]), _lib.ptr(self.ss[1]), B,
                                                    st), "b200_langevin_norm_sums")
             if self.pg is not None:
@@ -493,16 +494,18 @@ class FusedPCLoop:
                    "b200_sde_update")
         return n + 1
 
-    def _step_body(self, st, base_off):
-        """All launches of one PC step.  Noise offsets: (n_steps + 1) streams per step."""
+    def _step_body(self, st):
+        """All launches of one PC step.  Noise streams: update k of device step i draws Philox stream
+        base + i * 16 + k (the kernels add the device step counter themselves), so the launch arguments are the
+        same every step and the sequence can be captured once and replayed."""
         n = 0
         k = 0
         if self.corr:
             for _ in range(self.n_steps):
-                n += self._corrector(st, base_off + k)
+                n += self._corrector(st, self.offset_base + k)
                 k += 1
         if self.pred:
-            n += self._predictor(st, base_off + k)
+            n += self._predictor(st, self.offset_base + k)
         _lib.check(self.lib.b200_step_advance(_lib.ptr(self.step_dev), 1, st), "b200_step_advance")
         return n + 1
 
@@ -510,24 +513,41 @@ class FusedPCLoop:
     def reset(self, x0=None):
         self.step_dev.zero_()
         self.step_host = 0
-        self.offset = 0
         if x0 is not None:
             self.x.copy_(x0)
 
     def step(self):
-        """One PC step on the current stream.  Graph replay is not used when noise is injected or the Philox
-        offset must advance (offsets are baked into a captured graph), i.e. the graph path re-captures per offset
-        block; see `run`."""
-        st = _lib.stream()
-        n = self._step_body(st, self.offset)
-        self.offset += self.n_steps + 1
+        """One PC step launched eagerly on the current stream."""
+        n = self._step_body(_lib.stream())
         self.step_host += 1
         self.launches_per_step = n
         return n
 
+    def _graphable(self):
+        return (self.use_graph and NOISE_FN is None and self.pg is None and self.scaled is None
+                and self.n_steps + 1 <= 16)
+
     def run(self, n_iters):
-        for _ in range(n_iters):
+        """n_iters PC steps.  After one eager step (lazy initialisation of kernels / TMA descriptors) the step is
+        captured into a CUDA graph and replayed: no per-launch host cost inside the loop."""
+        if n_iters <= 0:
+            return 0
+        if not self._graphable() or n_iters < 3:
+            for _ in range(n_iters):
+                self.step()
+            return n_iters * self.launches_per_step
+        if self.graph is None:
             self.step()
+            n_iters -= 1
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._step_body(_lib.stream())
+            # capture records the launches without running them
+            self.graph = g
+        for _ in range(n_iters):
+            self.graph.replay()
+        self.step_host += n_iters
+        return (n_iters + 1) * self.launches_per_step
 
 
 def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,

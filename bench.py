@@ -274,16 +274,14 @@ def run_b200(a):
     # ---- device-resident timing: W warm-up + K timed PC steps -------------------------------------------------
     x0 = torch.randn(shape, device=dev) * sde.sigma_max
     loop.reset(x0)
-    for _ in range(a.warmup):
-        loop.step()
+    loop.run(max(a.warmup, 3))        # >= 3: one eager step + CUDA-graph capture + replays (single-GPU runs)
     barrier()
     clocks = ClockSampler(local)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    launches = 0
-    for _ in range(a.steps):
-        launches += loop.step()
+    loop.run(a.steps)
+    launches = a.steps * loop.launches_per_step
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)

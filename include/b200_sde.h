@@ -67,9 +67,10 @@ int b200_ns_cip_advect(float* out, const float* field, const float* vel, long lo
  * replaces the elementwise/reduction torch calls of sampling.py:181-187, 195-200, 213-233, 262-282, 299-319.
  * x, score, z, x_mean: [B, n_per] fp32.  z == NULL -> Philox4x32-10 noise generated in registers from
  * (seed, offset, elem_base + element index); elem_base (multiple of 4) is the shard's global element offset.
- * `step` != NULL -> coefficient index is *step for every sample (per-step tables, CUDA-graph friendly). */
+ * `step` != NULL -> coefficient index is *step for every sample (per-step tables) and the Philox stream id becomes
+ * offset + *step * 16, so a captured CUDA graph draws fresh noise on every replay. */
 int b200_sample_sumsq(float* ss_score, float* ss_noise, const float* score, const float* z, int B, long long n_per,
-                      uint64_t seed, uint64_t offset, long long elem_base, cudaStream_t stream);
+                      uint64_t seed, uint64_t offset, long long elem_base, const int* step, cudaStream_t stream);
 int b200_langevin_norm_sums(float* sums2, const float* ss_score, const float* ss_noise, int B, cudaStream_t stream);
 int b200_sde_update(float* x, float* x_mean, const float* score, const float* z, const float* a, const float* b,
                     const float* c, const int* step, int langevin, const float* norm_sums, float inv_batch_total,

@@ -132,3 +132,25 @@ def test_registry_contract():
     assert sampling.get_corrector("langevin").__name__ == "LangevinCorrector"
     with pytest.raises(ValueError):
         sampling.register_predictor(name="euler_maruyama")(sampling.EulerMaruyamaPredictor)
+
+
+def test_graph_replay_equals_eager(cuda):
+    """A PC step captured into a CUDA graph and replayed gives the same bits as eager launches (fused Philox noise:
+    the device step counter selects the stream, so frozen kernel arguments still draw fresh noise)."""
+    from b_pinn_kalman_filter_b200 import sampling, sde_lib
+    c = cases.pc_case("ve_rd_langevin")
+    m = _model(c["cfg"], c["sd"], cuda, "bf16")
+    sde = sde_lib.VESDE(c["cfg"].model.sigma_min, c["cfg"].model.sigma_max, 9)
+    outs = []
+    for use_graph in (False, True):
+        loop = sampling.FusedPCLoop(m, sde, c["shape"], sampling.ReverseDiffusionPredictor, sampling.LangevinCorrector,
+                                    0.16, 1, False, True, 1e-5, use_graph=use_graph, seed=7)
+        x0 = torch.full(c["shape"], 3.0, device=cuda)
+        loop.reset(x0)
+        loop.run(9)
+        torch.cuda.synchronize()
+        assert (loop.graph is not None) == use_graph
+        outs.append(loop.x.clone())
+    assert torch.isfinite(outs[0]).all()
+    assert torch.equal(outs[0], outs[1])
+    assert not torch.equal(outs[0], torch.full(c["shape"], 3.0, device=cuda))
