@@ -15,8 +15,8 @@
 //   B tile (BN output channels x 64 k) = a 2-D TMA box over the packed weights [Cout][taps*(C1+C2)].
 //   D tile (128 x BN fp32) lives in TMEM; two accumulator buffers so the epilogue of tile i overlaps the MMAs of
 //     tile i+1.
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected thread),
-// warps 2..5 = epilogue (tcgen05.ld -> bias/temb/residual/scale -> bf16 -> global).  Persistent: grid = min(tiles,
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected thread),
+// warps 2..9 = epilogue (tcgen05.ld -> bias/temb/residual/scale -> bf16 -> global).  Persistent: grid = min(tiles,
 // 148), static round-robin tile schedule.
 #include <mutex>
 #include <unordered_map>
@@ -28,7 +28,7 @@ namespace b200 {
 
 constexpr int TC_BM = 128;      // pixels per tile (UMMA M)
 constexpr int TC_BK = 64;       // channels per stage (64 bf16 = 128 B = one swizzle row)
-constexpr int TC_THREADS = 192;
+constexpr int TC_THREADS = 320;
 
 struct ConvTcParams {
   int B, H, W;                  // activation extent (stride 1: output extent too)
@@ -84,7 +84,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA1) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
@@ -160,8 +160,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       }
     }
   } else {
-    // ================= epilogue warps (2..5) =================
+    // ================= epilogue warps (2..9): two per TMEM lane quadrant, each takes half of the columns ==========
     const int q = warp & 3;                        // TMEM lane quadrant this warp may read
+    const int half = (warp - 2) >> 2;
     const int m_local = q * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -181,7 +182,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
         uint32_t r[16];
         tc_ld16(t_addr, r);
         tc_wait_ld();
-        if (valid) {
+        if (valid && half == 0) {
           const float mul = (p.sample_mul ? __ldg(p.sample_mul + b) : 1.0f) * p.out_scale;
           float* op = p.out_nchw + (((size_t)b * p.cout_true) * p.H + h) * p.W + w;
 #pragma unroll
@@ -190,10 +191,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               op[(size_t)j * p.H * p.W] = (__uint_as_float(r[j]) + (bs ? __ldg(bs + j) : 0.0f)) * mul;
         }
       } else {
+      constexpr int CH = BN / 2;                       // columns per epilogue warp (two warps share a lane quadrant)
+      const int cbeg = half * CH;
+      uint4 rv[4];
+      if (p.res && valid) {
+        const uint4* rp = reinterpret_cast<const uint4*>(p.res + row + cbeg);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) rv[j] = __ldg(rp + j);
+      }
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      for (int c0 = cbeg; c0 < cbeg + CH; c0 += 32) {
         uint32_t r[32];
         tc_ld32(t_addr + c0, r);
+        uint4 rn[4];                                     // residual of the NEXT chunk: in flight during this one
+        const bool more = c0 + 32 < cbeg + CH;
+        if (p.res && valid && more) {
+          const uint4* rp = reinterpret_cast<const uint4*>(p.res + row + c0 + 32);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) rn[j] = __ldg(rp + j);
+        }
         tc_wait_ld();
         if (valid) {
           float v[32];
@@ -214,11 +230,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             }
           }
           if (p.res) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.res + row + c0);
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              const uint4 t = __ldg(rp + j);
-              const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&t);
+              const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&rv[j]);
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
                 const float2 f = __bfloat1622float2(hh[i]);
@@ -236,6 +250,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               hh[i] = __floats2bfloat162_rn(v[j * 8 + 2 * i] * p.out_scale, v[j * 8 + 2 * i + 1] * p.out_scale);
             op[j] = t;
           }
+        }
+        if (more) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) rv[j] = rn[j];
         }
       }
       }
