@@ -55,14 +55,18 @@ struct TcSmem {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;
-  static constexpr int BAR_OFF = STAGES * STAGE_BYTES;
+  // output staging for the TMA-store epilogue: BN/64 boxes of [128 pixels x 64 channels] bf16 (SW128), EPI 0 only
+  static constexpr int OUT_OFF = STAGES * STAGE_BYTES;
+  static constexpr int OUT_BYTES = (BN >= 128) ? TC_BM * 128 * 2 : 0;   // 128 columns per pass (2 passes for BN = 256)
+  static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;           // barriers + tmem slot, + slack for 1024 B alignment
 };
 
 template <int BN, int EPI>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
-               const __grid_constant__ CUtensorMap mapW, const ConvTcParams p) {
+               const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapOut,
+               const ConvTcParams p) {
   using S = TcSmem<BN>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -191,8 +195,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               op[(size_t)j * p.H * p.W] = (__uint_as_float(r[j]) + (bs ? __ldg(bs + j) : 0.0f)) * mul;
         }
       } else {
-      constexpr int CH = BN / 2;                       // columns per epilogue warp (two warps share a lane quadrant)
-      const int cbeg = half * CH;
+      constexpr int CH = 64;                           // columns per warp per pass (two warps share a lane quadrant)
+#pragma unroll 1
+      for (int pass = 0; pass < BN / 128; ++pass) {
+      const int cbeg = pass * 128 + half * CH;
+      if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");  // staging buffer free (the previous store has read it)
       uint4 rv[4];
       if (p.res && valid) {
         const uint4* rp = reinterpret_cast<const uint4*>(p.res + row + cbeg);
@@ -240,7 +248,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               }
             }
           }
-          uint4* op = reinterpret_cast<uint4*>(p.out + row + c0);
+          // stage into the [128 x 64] SW128 box of this 64-channel group: 16-byte unit u of row r sits at u ^ (r & 7)
+          uint8_t* srow = smem_raw + (base - smem_u32(smem_raw)) + S::OUT_OFF + ((c0 >> 6) & 1) * (TC_BM * 128) + m_local * 128;
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 t;
@@ -248,7 +257,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 #pragma unroll
             for (int i = 0; i < 4; ++i)
               hh[i] = __floats2bfloat162_rn(v[j * 8 + 2 * i] * p.out_scale, v[j * 8 + 2 * i + 1] * p.out_scale);
-            op[j] = t;
+            const int unit = ((c0 & 63) >> 3) + j;
+            *reinterpret_cast<uint4*>(srow + ((unit ^ (m_local & 7)) << 4)) = t;
           }
         }
         if (more) {
@@ -256,13 +266,29 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           for (int j = 0; j < 4; ++j) rv[j] = rn[j];
         }
       }
+      if (pass == BN / 128 - 1) {                      // last TMEM read of this tile done: hand the accumulator back
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(acc));
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      fence_proxy_async_smem();                        // generic-proxy smem writes -> visible to the TMA store
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 64) {
+        tma_store_4d(base + S::OUT_OFF, &mapOut, nt * BN + pass * 128, w0, h0, b0);
+        tma_store_4d(base + S::OUT_OFF + TC_BM * 128, &mapOut, nt * BN + pass * 128 + 64, w0, h0, b0);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+      }
+      }
+      if constexpr (EPI == 1) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(acc));
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
+  if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -348,7 +374,8 @@ bool tile_box(int B, int H, int W, int& TW, int& TH, int& TB, int& tiles_w, int&
 }
 
 template <int BN, int EPI>
-int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const ConvTcParams& p, cudaStream_t st) {
+int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
+           const ConvTcParams& p, cudaStream_t st) {
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
@@ -357,7 +384,7 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
   if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
-  conv_tc_kernel<BN, EPI><<<grid, TC_THREADS, TcSmem<BN>::TOTAL, st>>>(a1, a2, w, p);
+  conv_tc_kernel<BN, EPI><<<grid, TC_THREADS, TcSmem<BN>::TOTAL, st>>>(a1, a2, w, om, p);
   B200_RETURN_LAST();
 }
 
@@ -427,6 +454,9 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   else a2 = a1;
   rc = weight_map(&wm, w, Cout, Ktot, BN);          // rows beyond Cout are zero-filled by TMA (head: 3 of 16)
   if (rc) return rc;
-  if (out_mode == 1) return launch<16, 1>(a1, a2, wm, p, st);
-  return BN == 256 ? launch<256, 0>(a1, a2, wm, p, st) : launch<128, 0>(a1, a2, wm, p, st);
+  if (out_mode == 1) return launch<16, 1>(a1, a2, wm, a1, p, st);
+  CUtensorMap om;
+  rc = act_map(&om, out, B, H, W, Cout, p.TW, p.TH, p.TB);
+  if (rc) return rc;
+  return BN == 256 ? launch<256, 0>(a1, a2, wm, om, p, st) : launch<128, 0>(a1, a2, wm, om, p, st);
 }
