@@ -33,7 +33,7 @@ constexpr int TC_THREADS = 320;
 struct ConvTcParams {
   int B, H, W;                  // activation extent (stride 1: output extent too)
   int C1, C2, Cout;             // Cout = channels of the output tensor (multiple of BN)
-  int taps_w, pad;              // KW (1 or 3) -- KH == KW; pad = KW / 2
+  int taps_w, pad, stride;      // KW (1 or 3) -- KH == KW; pad = KW / 2 (0 for the stride-2 VALID convs)
   int TW, TH, TB;               // tile box: TW * TH * TB == 128
   int tiles_w, tiles_h;         // M tiles per image row / per image column (TB == 1), else 1
   int num_m, num_n;             // tile counts
@@ -127,8 +127,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             const uint32_t sa = base + stage * S::STAGE_BYTES, sb = sa + S::A_BYTES;
             mbar_expect_tx(full_bar(stage), S::STAGE_BYTES);
             const int c = kb * TC_BK;
-            if (c < p.C1) tma_load_4d(sa, &mapA1, full_bar(stage), c, w0 + s - p.pad, h0 + r - p.pad, b0);
-            else tma_load_4d(sa, &mapA2, full_bar(stage), c - p.C1, w0 + s - p.pad, h0 + r - p.pad, b0);
+            if (c < p.C1) tma_load_4d(sa, &mapA1, full_bar(stage), c, w0 * p.stride + s - p.pad, h0 * p.stride + r - p.pad, b0);
+            else tma_load_4d(sa, &mapA2, full_bar(stage), c - p.C1, w0 * p.stride + s - p.pad, h0 * p.stride + r - p.pad, b0);
             tma_load_2d(sb, &mapW, full_bar(stage), tap * Ctot + c, nt * BN);
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
@@ -339,11 +339,13 @@ std::mutex g_map_mu;
 std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 
 // 4-D map over a channels-last activation [B, H, W, C] (bf16); box {64, TW, TH, TB}.
-int act_map(CUtensorMap* out, const void* ptr, int B, int H, int W, int C, int TW, int TH, int TB) {
+int act_map(CUtensorMap* out, const void* ptr, int B, int H, int W, int C, int TW, int TH, int TB, int estride = 1) {
   const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)B};
   const uint64_t strides[3] = {(uint64_t)C * 2, (uint64_t)W * C * 2, (uint64_t)H * W * C * 2};
-  const uint32_t box[4] = {(uint32_t)TC_BK, (uint32_t)TW, (uint32_t)TH, (uint32_t)TB};
-  return tc_tensor_map(out, ptr, 4, dims, strides, box, 0);
+  // with an element stride s the box is given in traversed elements: TW*s columns load TW pixels
+  const uint32_t box[4] = {(uint32_t)TC_BK, (uint32_t)(TW * estride), (uint32_t)(TH * estride), (uint32_t)TB};
+  const uint32_t es[4] = {1, (uint32_t)estride, (uint32_t)estride, 1};
+  return tc_tensor_map(out, ptr, 4, dims, strides, box, 0, es);
 }
 
 // 2-D map over packed weights [Cout][Ktot] (bf16, K contiguous); box {64, BN}.
@@ -392,10 +394,11 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
 
 namespace b200 {
 int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides,
-                  const uint32_t* box, int l2_256) {
+                  const uint32_t* box, int l2_256, const uint32_t* estr) {
   MapKey key;
   for (int i = 0; i < 14; ++i) key.v[i] = 0;
   key.v[0] = (uint64_t)ptr; key.v[1] = (uint64_t)rank | ((uint64_t)l2_256 << 8);
+  if (estr) for (int i = 0; i < rank; ++i) key.v[1] |= (uint64_t)estr[i] << (16 + 8 * i);
   for (int i = 0; i < rank; ++i) { key.v[2 + i] = dims[i]; key.v[6 + i] = box[i]; }
   for (int i = 0; i + 1 < rank; ++i) key.v[10 + i] = strides[i];
   {
@@ -407,7 +410,7 @@ int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* d
   if (!enc) return B200_ERR_DRIVER;
   cuuint64_t d[4], st[3];
   cuuint32_t bx[4], es[4] = {1, 1, 1, 1};
-  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; if (estr) es[i] = estr[i]; }
   for (int i = 0; i + 1 < rank; ++i) st[i] = strides[i];
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -438,7 +441,7 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1, out_mode)) return B200_ERR_UNSUPPORTED;
   if (out_mode == 1 && (temb || res)) return B200_ERR_UNSUPPORTED;
   ConvTcParams p;
-  p.B = B; p.H = H; p.W = W; p.C1 = C1; p.C2 = C2; p.Cout = Cout; p.taps_w = ksize; p.pad = ksize / 2;
+  p.B = B; p.H = H; p.W = W; p.C1 = C1; p.C2 = C2; p.Cout = Cout; p.taps_w = ksize; p.pad = ksize / 2; p.stride = 1;
   tile_box(B, H, W, p.TW, p.TH, p.TB, p.tiles_w, p.tiles_h);
   p.num_m = p.TB > 1 ? (B + p.TB - 1) / p.TB : B * p.tiles_w * p.tiles_h;
   int BN = out_mode == 1 ? 16 : ((Cout % 256 == 0) ? 256 : 128);
@@ -459,4 +462,38 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   rc = act_map(&om, out, B, H, W, Cout, p.TW, p.TH, p.TB);
   if (rc) return rc;
   return BN == 256 ? launch<256, 0>(a1, a2, wm, om, p, st) : launch<128, 0>(a1, a2, wm, om, p, st);
+}
+
+// 3x3 stride-2 VALID convolution (zero fill beyond the input extent) on the same kernel: the TMA box walks the input
+// with element strides {1, 2, 2, 1}.  Covers conv_downsample_2d's F.conv2d(stride=2) on the FIR-padded (H+1)x(W+1)
+// tensor (models/up_or_down_sampling.py:174-178) and DDPM's pad(0,1,0,1) + conv3x3 stride 2 (models/layers.py:596-608).
+extern "C" int b200_conv2d_tc_s2_supported(int C, int B, int Ho, int Wo, int Cout) {
+  int TW, TH, TB, tw, th;
+  if (C <= 0 || C % TC_BK || Cout <= 0 || Cout % 128 || B <= 0) return 0;
+  if (!tile_box(B, Ho, Wo, TW, TH, TB, tw, th)) return 0;
+  return (TW * 2 <= 256 && TH * 2 <= 256) ? 1 : 0;
+}
+
+extern "C" int b200_conv2d_tc_s2(const void* x, int C, const void* w, const float* bias, const void* res,
+                                 float out_scale, void* out, int B, int Hin, int Win, int Ho, int Wo, int Cout,
+                                 cudaStream_t st) {
+  if (!x || !w || !out) return B200_ERR_ARG;
+  if (!b200_conv2d_tc_s2_supported(C, B, Ho, Wo, Cout)) return B200_ERR_UNSUPPORTED;
+  ConvTcParams p;
+  p.B = B; p.H = Ho; p.W = Wo; p.C1 = C; p.C2 = 0; p.Cout = Cout; p.taps_w = 3; p.pad = 0; p.stride = 2;
+  tile_box(B, Ho, Wo, p.TW, p.TH, p.TB, p.tiles_w, p.tiles_h);
+  p.num_m = p.TB > 1 ? (B + p.TB - 1) / p.TB : B * p.tiles_w * p.tiles_h;
+  int BN = (Cout % 256 == 0) ? 256 : 128;
+  if (BN == 256 && p.num_m * (Cout / 256) < B200_NUM_SMS) BN = 128;
+  p.num_n = Cout / BN;
+  p.bias = bias; p.temb = nullptr; p.temb_stride = 0; p.res = (const bf16*)res; p.out_scale = out_scale;
+  p.out = (bf16*)out; p.out_nchw = nullptr; p.sample_mul = nullptr; p.cout_true = Cout;
+  CUtensorMap a1, wm, om;
+  int rc = act_map(&a1, x, B, Hin, Win, C, p.TW, p.TH, p.TB, 2);
+  if (rc) return rc;
+  rc = weight_map(&wm, w, Cout, 9 * C, BN);
+  if (rc) return rc;
+  rc = act_map(&om, out, B, Ho, Wo, Cout, p.TW, p.TH, p.TB);
+  if (rc) return rc;
+  return BN == 256 ? launch<256, 0>(a1, a1, wm, om, p, st) : launch<128, 0>(a1, a1, wm, om, p, st);
 }

@@ -103,6 +103,6 @@ __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.p
 // Cached cuTensorMapEncodeTiled (bf16, 128B swizzle, zero OOB fill); rank <= 4, strides in bytes for dims 1..rank-1.
 // Returns B200_OK / B200_ERR_DRIVER.  Descriptors depend only on (pointer, extents, box), so they are memoised.
 int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides,
-                  const uint32_t* box, int l2_256);
+                  const uint32_t* box, int l2_256, const uint32_t* elem_strides = nullptr);
 
 }  // namespace b200

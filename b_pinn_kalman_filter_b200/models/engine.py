@@ -429,6 +429,11 @@ class ScoreEngine:
     # ---- kernel selection -------------------------------------------------------------------------------------
     def emit_conv(self, b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, stride, pad, key):
         from . import tc
+        if (self.use_tc and stride == 2 and ksize == 3 and tuple(pad) == (0, 0) and x2 is None and temb_ptr is None
+                and tc.s2_supported(b, x, out)):
+            tc.emit_s2(b, x, w, bias, res, out_scale, out, self.conv_flops(b, x, x2, out, ksize))
+            self.tc_convs += 1
+            return
         if self.use_tc and tc.conv_supported(b, x, x2, out, ksize, stride, tuple(pad)):
             tc.emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, self.conv_flops(b, x, x2, out, ksize))
             self.tc_convs += 1

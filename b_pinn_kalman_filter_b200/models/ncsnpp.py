@@ -48,6 +48,8 @@ def build_ncsnpp(b, config):
     # ---- input ----------------------------------------------------------------------------------------------
     x = net.input_image(channels, size, size, rescale=not config.data.centered)
     pyramid_in = x if progressive_input != "none" else None
+    if progressive_input == "residual":
+        pyramid_in = net.x_stem      # 64-wide on the tensor-core path so that the FIR conv-downsample runs there
 
     hs = [net.conv3x3(net.x_stem, net.next_module(), nf)]
     hs_c = [nf]

@@ -9,6 +9,9 @@ _lib.register_signature("b200_conv2d_tc", [c_vp, c_int, c_vp, c_int, c_vp, c_vp,
 _lib.register_signature("b200_attention_tc_supported", [c_int, c_int])
 _lib.register_signature("b200_attention_tc", [c_vp, c_vp, c_int, c_int, c_int, c_float, c_vp])
 
+_lib.register_signature("b200_conv2d_tc_s2_supported", [c_int] * 5)
+_lib.register_signature("b200_conv2d_tc_s2", [c_vp, c_int, c_vp, c_vp, c_vp, c_float, c_vp] + [c_int] * 6 + [c_vp])
+
 ENABLED = True
 
 
@@ -42,3 +45,12 @@ def attention_supported(L, C):
 
 def emit_attention(b, qkv, out, L, C):
     b.emit("b200_attention_tc", qkv, out, b.B, L, C, float(int(C) ** (-0.5)), flops=4 * b.B * L * L * C)
+
+
+def s2_supported(b, x, out):
+    return ENABLED and bool(_lib.lib().b200_conv2d_tc_s2_supported(x.C, b.B, out.H, out.W, out.C))
+
+
+def emit_s2(b, x, w, bias, res, out_scale, out, flops):
+    b.emit("b200_conv2d_tc_s2", x, x.C, w.data_ptr(), bias.data_ptr(), res, out_scale, out, b.B, x.H, x.W, out.H, out.W,
+           out.C, flops=flops, tag="3x3/2 %dx%d %d->%d" % (x.H, x.W, x.C, out.C))

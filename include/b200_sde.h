@@ -117,6 +117,12 @@ int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int 
 int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias, const float* temb,
                    int temb_stride, const void* res, float out_scale, void* out, int out_mode, const float* sample_mul,
                    int B, int H, int W, int Cout, int ksize, cudaStream_t stream);
+/* 3x3 stride-2 VALID conv (zero beyond the input extent) on the same tensor-core kernel (TMA element strides):
+ * F.conv2d(stride=2) of conv_downsample_2d (models/up_or_down_sampling.py:174-178) on the FIR-padded input, and
+ * DDPM's pad(0,1,0,1)+conv3x3/2 (models/layers.py:596-608).  x [B,Hin,Win,C] bf16, out [B,Ho,Wo,Cout] bf16. */
+int b200_conv2d_tc_s2_supported(int C, int B, int Ho, int Wo, int Cout);
+int b200_conv2d_tc_s2(const void* x, int C, const void* w, const float* bias, const void* res, float out_scale,
+                      void* out, int B, int Hin, int Win, int Ho, int Wo, int Cout, cudaStream_t stream);
 /* softmax(q k^T scale) v per image on CUDA cores (models/layerspp.py:82-86); ld* = row strides in elements */
 int b200_attention_simt(const void* q, const void* k, const void* v, void* out, int dtype, int B, int L, int C,
                         int ldq, int ldk, int ldv, int ldo, float scale, cudaStream_t stream);

@@ -120,3 +120,32 @@ def test_conv_tc_head_nchw(cuda, B, H, C, Cout, k):
     ref = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), bias, padding=k // 2)
     ref = ref * mul[:, None, None, None]
     assert (out - ref).abs().max().item() <= 1e-4 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("B,Hin,C,Cout,res", [(3, 33, 64, 128, True), (5, 17, 128, 256, True), (9, 9, 256, 256, False),
+                                              (2, 64, 128, 128, False)])
+def test_conv_tc_stride2(cuda, B, Hin, C, Cout, res):
+    """3x3 stride-2 VALID conv with zero fill beyond the input (FIR conv-downsample / DDPM downsample)."""
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import tc  # noqa: F401
+    Ho = Hin // 2
+    g = torch.Generator(device="cpu").manual_seed(Hin + C)
+    x = torch.randn(B, Hin, Hin, C, generator=g).to(cuda, torch.bfloat16)
+    w = (torch.randn(Cout, 3, 3, C, generator=g) / (9 * C) ** 0.5).to(cuda, torch.bfloat16)
+    bias = torch.randn(Cout, generator=g).to(cuda)
+    r = torch.randn(B, Ho, Ho, Cout, generator=g).to(cuda, torch.bfloat16) if res else None
+    out = torch.full((B, Ho, Ho, Cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+    lib = _lib.lib()
+    assert lib.b200_conv2d_tc_s2_supported(C, B, Ho, Ho, Cout) == 1
+    _lib.check(lib.b200_conv2d_tc_s2(_lib.ptr(x), C, _lib.ptr(w), _lib.ptr(bias), _lib.ptr(r), 0.5, _lib.ptr(out), B, Hin,
+                                     Hin, Ho, Ho, Cout, _lib.stream()), "conv2d_tc_s2")
+    torch.cuda.synchronize()
+    xin = x.float().permute(0, 3, 1, 2)
+    pad = 2 * Ho + 1 - Hin                     # even inputs: one zero row/column at the bottom/right (F.pad(0,1,0,1))
+    xin = torch.nn.functional.pad(xin, (0, pad, 0, pad))
+    ref = torch.nn.functional.conv2d(xin, w.float().permute(0, 3, 1, 2), bias, stride=2).permute(0, 2, 3, 1)
+    if res:
+        ref = ref + r.float()
+    ref = ref * 0.5
+    assert torch.isfinite(out).all()
+    assert ((out.float() - ref).norm() / ref.norm()).item() < 4e-3
