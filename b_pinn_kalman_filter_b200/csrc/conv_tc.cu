@@ -46,6 +46,10 @@ struct ConvTcParams {
   float* out_nchw;              // [B, cout_true, H, W] fp32, * sample_mul[b]  (EPI 1: network head, ncsnpp.py:371-379)
   const float* sample_mul;
   int cout_true;
+  // optional by-product for the consumer GroupNorm: per-(image, slot, channel) sum and sum of squares of the bf16
+  // OUTPUT values, [B][slots][Cout][2] fp32; slots = 2 * tiles per image when a tile lies inside one image, else 1
+  float* stats;
+  int stat_slots;
 };
 
 template <int BN>
@@ -278,6 +282,30 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
         tma_store_4d(base + S::OUT_OFF + TC_BM * 128, &mapOut, nt * BN + pass * 128 + 64, w0, h0, b0);
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
+      if (p.stats) {
+        // column sums over the staged tile: thread = (column, 64-row half); fixed order -> bit-reproducible
+        const int et = threadIdx.x - 64, col = et & 127, rh = et >> 7;
+        const uint8_t* sbox = smem_raw + (base - smem_u32(smem_raw)) + S::OUT_OFF + (col >> 6) * (TC_BM * 128);
+        const int unit = (col & 63) >> 3, sub = (col & 7) * 2;
+        const int rows_img = p.TW * p.TH;                  // rows of one image inside the tile (128 when TB == 1)
+        const int seg = rows_img < 64 ? rows_img : 64;
+        const int ch = nt * BN + pass * 128 + col;
+        for (int r0 = rh * 64; r0 < rh * 64 + 64; r0 += seg) {
+          float s1 = 0.f, s2 = 0.f;
+          for (int r = r0; r < r0 + seg; ++r) {
+            const bf16 hv = *reinterpret_cast<const bf16*>(sbox + r * 128 + ((unit ^ (r & 7)) << 4) + sub);
+            const float f = __bfloat162float(hv);
+            s1 += f; s2 = fmaf(f, f, s2);
+          }
+          int bi, slot;
+          if (p.TB > 1) { bi = b0 + r0 / rows_img; slot = 0; }
+          else { bi = b0; slot = ((h0 / p.TH) * p.tiles_w + w0 / p.TW) * 2 + rh; }
+          if (bi < p.B) {
+            float* sp = p.stats + (((size_t)bi * p.stat_slots + slot) * p.Cout + ch) * 2;
+            sp[0] = s1; sp[1] = s2;
+          }
+        }
+      }
       }
       }
       if constexpr (EPI == 1) {
@@ -423,6 +451,13 @@ int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* d
 }
 }  // namespace b200
 
+// slots per image of the `stats` by-product for an output of extent H x W (0: shape not supported)
+extern "C" int b200_conv2d_tc_stat_slots(int B, int H, int W) {
+  int TW, TH, TB, tw, th;
+  if (B <= 0 || !tile_box(B, H, W, TW, TH, TB, tw, th)) return 0;
+  return TB > 1 ? 1 : 2 * tw * th;
+}
+
 extern "C" int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride,
                                         int out_mode) {
   int TW, TH, TB, tw, th;
@@ -435,8 +470,8 @@ extern "C" int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int
 
 extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
                               const float* temb, int temb_stride, const void* res, float out_scale, void* out,
-                              int out_mode, const float* sample_mul, int B, int H, int W, int Cout, int ksize,
-                              cudaStream_t st) {
+                              int out_mode, const float* sample_mul, float* stats, int B, int H, int W, int Cout,
+                              int ksize, cudaStream_t st) {
   if (!x1 || !w || !out || (C2 > 0 && !x2)) return B200_ERR_ARG;
   if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1, out_mode)) return B200_ERR_UNSUPPORTED;
   if (out_mode == 1 && (temb || res)) return B200_ERR_UNSUPPORTED;
@@ -449,6 +484,7 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   p.num_n = out_mode == 1 ? 1 : Cout / BN;
   p.bias = bias; p.temb = temb; p.temb_stride = temb_stride; p.res = (const bf16*)res; p.out_scale = out_scale;
   p.out = (bf16*)out; p.out_nchw = (float*)out; p.sample_mul = sample_mul; p.cout_true = Cout;
+  p.stats = out_mode == 0 ? stats : nullptr; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h;
   const int Ktot = ksize * ksize * (C1 + C2);
   CUtensorMap a1, a2, wm;
   int rc = act_map(&a1, x1, B, H, W, C1, p.TW, p.TH, p.TB);
@@ -475,8 +511,8 @@ extern "C" int b200_conv2d_tc_s2_supported(int C, int B, int Ho, int Wo, int Cou
 }
 
 extern "C" int b200_conv2d_tc_s2(const void* x, int C, const void* w, const float* bias, const void* res,
-                                 float out_scale, void* out, int B, int Hin, int Win, int Ho, int Wo, int Cout,
-                                 cudaStream_t st) {
+                                 float out_scale, void* out, float* stats, int B, int Hin, int Win, int Ho, int Wo,
+                                 int Cout, cudaStream_t st) {
   if (!x || !w || !out) return B200_ERR_ARG;
   if (!b200_conv2d_tc_s2_supported(C, B, Ho, Wo, Cout)) return B200_ERR_UNSUPPORTED;
   ConvTcParams p;
@@ -488,6 +524,7 @@ extern "C" int b200_conv2d_tc_s2(const void* x, int C, const void* w, const floa
   p.num_n = Cout / BN;
   p.bias = bias; p.temb = nullptr; p.temb_stride = 0; p.res = (const bf16*)res; p.out_scale = out_scale;
   p.out = (bf16*)out; p.out_nchw = nullptr; p.sample_mul = nullptr; p.cout_true = Cout;
+  p.stats = stats; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h;
   CUtensorMap a1, wm, om;
   int rc = act_map(&a1, x, B, Hin, Win, C, p.TW, p.TH, p.TB, 2);
   if (rc) return rc;

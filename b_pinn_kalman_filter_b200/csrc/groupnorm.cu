@@ -17,6 +17,9 @@ struct GnArgs {
   float* partial;                               // [B, nsplit, G, 2]
   const float* gamma; const float* beta; float eps; int act;  // act: 0 none, 1 silu
   void* out;                                    // [B, HW, C1+C2]
+  // alternative to `partial`: per-channel statistics written by the producing convolutions' epilogues
+  // (conv_tc.cu `stats`): st_i = [B][T_i][C_i][2]
+  const float* st1; const float* st2; int T1, T2;
 };
 
 // Thread layout shared by both kernels: `nthr` threads sweep pixels; nthr is a multiple of CV = C/8 so that each
@@ -77,8 +80,28 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(GnArgs a) {
   const int C = a.C1 + a.C2, CV = C >> 3;
   const int b = blockIdx.x / a.nsplit, sp = blockIdx.x % a.nsplit;
   const int cpg = C / a.G;
+  double* chs = reinterpret_cast<double*>(sh + 2 * a.G);      // [C] sums, [C] sums of squares (stats path only)
+  if (a.st1) {
+    // fold the slots per channel with all threads (coalesced over channels), then the channels per group
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const bool first = c < a.C1;
+      const float* base = first ? a.st1 + ((size_t)b * a.T1 * a.C1 + c) * 2
+                                : a.st2 + ((size_t)b * a.T2 * a.C2 + (c - a.C1)) * 2;
+      const int T = first ? a.T1 : a.T2, cs = first ? a.C1 : a.C2;
+      double ts = 0.0, tq = 0.0;
+      for (int k = 0; k < T; ++k) {
+        const float2 v = __ldg(reinterpret_cast<const float2*>(base + (size_t)k * cs * 2));
+        ts += (double)v.x; tq += (double)v.y;
+      }
+      chs[c] = ts; chs[C + c] = tq;
+    }
+    __syncthreads();
+  }
   for (int g = threadIdx.x; g < a.G; g += blockDim.x) {
     double ts = 0.0, tq = 0.0;
+    if (a.st1) {
+      for (int c = g * cpg; c < (g + 1) * cpg; ++c) { ts += chs[c]; tq += chs[C + c]; }   // may straddle the sources
+    } else
     for (int k = 0; k < a.nsplit; ++k) {
       const float* o = a.partial + (((size_t)b * a.nsplit + k) * a.G + g) * 2;
       ts += (double)o[0]; tq += (double)o[1];
@@ -162,6 +185,7 @@ static int gn_fill(GnArgs& a, const void* x1, int C1, const void* x2, int C2, in
   if (C1 % 8 || C2 % 8 || C % G || gn_threads(C) == 0) return B200_ERR_UNSUPPORTED;
   a.x1 = x1; a.x2 = x2; a.C1 = C1; a.C2 = C2; a.B = B; a.HW = HW; a.G = G; a.nsplit = nsplit; a.partial = partial;
   a.gamma = nullptr; a.beta = nullptr; a.eps = 0.f; a.act = 0; a.out = nullptr;
+  a.st1 = nullptr; a.st2 = nullptr; a.T1 = 0; a.T2 = 0;
   return B200_OK;
 }
 
@@ -188,7 +212,31 @@ extern "C" int b200_gn_apply(const void* x1, int C1, const void* x2, int C2, int
   if (B == 0) return B200_OK;
   a.gamma = gamma; a.beta = beta; a.eps = eps; a.act = act; a.out = out;
   const int C = C1 + C2, thr = gn_threads(C);
-  const size_t smem = 2 * G * sizeof(float);
+  if (G % 2) return B200_ERR_UNSUPPORTED;              // keeps the double scratch 8-byte aligned
+  const size_t smem = 2 * G * sizeof(float) + 2 * C * sizeof(double);
+  if (dtype == B200_DT_F32) gn_apply_kernel<float><<<B * nsplit, thr, smem, st>>>(a);
+  else if (dtype == B200_DT_BF16) gn_apply_kernel<bf16><<<B * nsplit, thr, smem, st>>>(a);
+  else return B200_ERR_ARG;
+  B200_RETURN_LAST();
+}
+
+// GroupNorm(+SiLU) apply from the per-channel statistics the producing tensor-core convolutions leave behind
+// (b200_conv2d_tc `stats`): no statistics pass over the activation at all.
+extern "C" int b200_gn_apply_stats(const void* x1, int C1, const float* st1, int T1, const void* x2, int C2,
+                                   const float* st2, int T2, int dtype, int B, int HW, int G, int nsplit,
+                                   const float* gamma, const float* beta, float eps, int act, void* out,
+                                   cudaStream_t st) {
+  GnArgs a;
+  float dummy;
+  int rc = gn_fill(a, x1, C1, x2, C2, B, HW, G, nsplit, &dummy);
+  if (rc) return rc;
+  if (!out || !st1 || T1 <= 0 || (C2 > 0 && (!st2 || T2 <= 0))) return B200_ERR_ARG;
+  if (B == 0) return B200_OK;
+  a.partial = nullptr; a.st1 = st1; a.st2 = st2; a.T1 = T1; a.T2 = T2;
+  a.gamma = gamma; a.beta = beta; a.eps = eps; a.act = act; a.out = out;
+  const int C = C1 + C2, thr = gn_threads(C);
+  if (G % 2) return B200_ERR_UNSUPPORTED;              // keeps the double scratch 8-byte aligned
+  const size_t smem = 2 * G * sizeof(float) + 2 * C * sizeof(double);
   if (dtype == B200_DT_F32) gn_apply_kernel<float><<<B * nsplit, thr, smem, st>>>(a);
   else if (dtype == B200_DT_BF16) gn_apply_kernel<bf16><<<B * nsplit, thr, smem, st>>>(a);
   else return B200_ERR_ARG;

@@ -41,11 +41,13 @@ _TORCH_DT = {DT_F32: torch.float32, DT_BF16: torch.bfloat16}
 
 class Act:
     """A channels-last activation living in the workspace."""
-    __slots__ = ("t", "B", "H", "W", "C", "Ct")
+    __slots__ = ("t", "B", "H", "W", "C", "Ct", "producer", "stats")
 
     def __init__(self, t, B, H, W, C, Ct=None):
         self.t, self.B, self.H, self.W, self.C = t, B, H, W, C
         self.Ct = C if Ct is None else Ct   # channels that carry data (3-channel images live in 8-wide tensors)
+        self.producer = None                # (launch index, arg position) of the tensor-core conv that wrote it
+        self.stats = None                   # (pointer, slots) of its GroupNorm statistics by-product
 
     @property
     def ptr(self):
@@ -217,8 +219,15 @@ class Builder:
             return out
         HW = x.H * x.W
         ns = self.lib.b200_gn_nsplit(self.B, HW)
-        part = self.f32(self.B * ns * groups * 2)
         p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+        if self.e.use_tc and self.e.fuse_gn_stats and x.producer is not None and (x2 is None or x2.producer is not None):
+            from . import tc
+            s1, t1 = tc.request_stats(self, x)
+            s2, t2 = tc.request_stats(self, x2) if x2 is not None else (None, 0)
+            self.emit("b200_gn_apply_stats", x, x.C, s1, t1, p2, c2, s2, t2, self.dt, self.B, HW, groups, ns,
+                      self.e.dev(key + ".weight"), self.e.dev(key + ".bias"), 1e-6, 1 if act else 0, out)
+            return out
+        part = self.f32(self.B * ns * groups * 2)
         self.emit("b200_gn_partial", x, x.C, p2, c2, self.dt, self.B, HW, groups, ns, part.data_ptr())
         self.emit("b200_gn_apply", x, x.C, p2, c2, self.dt, self.B, HW, groups, ns, part.data_ptr(),
                   self.e.dev(key + ".weight"), self.e.dev(key + ".bias"), 1e-6, 1 if act else 0, out)
@@ -325,6 +334,7 @@ class ScoreEngine:
         self.precision = precision
         self.dt = {"bf16": DT_BF16, "fp32": DT_F32}[precision]
         self.use_tc = bool(use_tensor_cores) and self.dt == DT_BF16
+        self.fuse_gn_stats = True           # GroupNorm statistics as a by-product of the producing conv's epilogue
         self.workspace = Workspace(self.device)
         self.params = {}           # reference-layout fp32 tensors on device
         self._packed = {}

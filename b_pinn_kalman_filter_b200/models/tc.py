@@ -4,13 +4,16 @@ from .._lib import c_float, c_int, c_vp
 
 _lib.register_signature("b200_conv2d_tc_supported", [c_int] * 9)
 _lib.register_signature("b200_conv2d_tc", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_vp,
-                                           c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp])
+                                           c_int, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp])
 
 _lib.register_signature("b200_attention_tc_supported", [c_int, c_int])
 _lib.register_signature("b200_attention_tc", [c_vp, c_vp, c_int, c_int, c_int, c_float, c_vp])
 
 _lib.register_signature("b200_conv2d_tc_s2_supported", [c_int] * 5)
-_lib.register_signature("b200_conv2d_tc_s2", [c_vp, c_int, c_vp, c_vp, c_vp, c_float, c_vp] + [c_int] * 6 + [c_vp])
+_lib.register_signature("b200_conv2d_tc_s2", [c_vp, c_int, c_vp, c_vp, c_vp, c_float, c_vp, c_vp] + [c_int] * 6 + [c_vp])
+_lib.register_signature("b200_conv2d_tc_stat_slots", [c_int] * 3)
+_lib.register_signature("b200_gn_apply_stats", [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int,
+                                                c_int, c_int, c_vp, c_vp, c_float, c_int, c_vp, c_vp])
 
 ENABLED = True
 
@@ -25,8 +28,9 @@ def conv_supported(b, x, x2, out, ksize, stride, pad):
 def emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
     p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
     b.emit("b200_conv2d_tc", x, x.C, p2, c2, w.data_ptr(), bias.data_ptr(), temb_ptr, b.temb_stride, res, out_scale,
-           out, 0, None, b.B, x.H, x.W, out.C, ksize, flops=flops,
+           out, 0, None, None, b.B, x.H, x.W, out.C, ksize, flops=flops,
            tag="%dx%d %dx%d %d->%d" % (ksize, ksize, x.H, x.W, x.C + c2, out.C))
+    out.producer = (len(b.plan.ops) - 1, 13)      # (launch index, position of the `stats` argument)
 
 
 def head_supported(b, x, cout, ksize):
@@ -36,7 +40,7 @@ def head_supported(b, x, cout, ksize):
 
 def emit_head(b, x, w, bias, out_scale, out_ptr, sample_mul_ptr, cout, ksize, flops):
     b.emit("b200_conv2d_tc", x, x.C, None, 0, w.data_ptr(), bias.data_ptr(), None, 0, None, out_scale, out_ptr, 1,
-           sample_mul_ptr, b.B, x.H, x.W, cout, ksize, flops=flops)
+           sample_mul_ptr, None, b.B, x.H, x.W, cout, ksize, flops=flops)
 
 
 def attention_supported(L, C):
@@ -52,5 +56,18 @@ def s2_supported(b, x, out):
 
 
 def emit_s2(b, x, w, bias, res, out_scale, out, flops):
-    b.emit("b200_conv2d_tc_s2", x, x.C, w.data_ptr(), bias.data_ptr(), res, out_scale, out, b.B, x.H, x.W, out.H, out.W,
-           out.C, flops=flops, tag="3x3/2 %dx%d %d->%d" % (x.H, x.W, x.C, out.C))
+    b.emit("b200_conv2d_tc_s2", x, x.C, w.data_ptr(), bias.data_ptr(), res, out_scale, out, None, b.B, x.H, x.W, out.H,
+           out.W, out.C, flops=flops, tag="3x3/2 %dx%d %d->%d" % (x.H, x.W, x.C, out.C))
+    out.producer = (len(b.plan.ops) - 1, 7)
+
+
+def request_stats(b, act):
+    """Makes the tensor-core conv that produced `act` also write the GroupNorm statistics; returns (ptr, slots)."""
+    if act.stats is None:
+        T = _lib.lib().b200_conv2d_tc_stat_slots(b.B, act.H, act.W)
+        buf = b.f32(b.B * T * act.C * 2)
+        idx, pos = act.producer
+        fn, args, name = b.plan.ops[idx]
+        b.plan.ops[idx] = (fn, args[:pos] + (buf.data_ptr(),) + args[pos + 1:], name)
+        act.stats = (buf.data_ptr(), T)
+    return act.stats

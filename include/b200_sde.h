@@ -89,6 +89,9 @@ int b200_gn_partial(const void* x1, int C1, const void* x2, int C2, int dtype, i
 int b200_gn_apply(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G, int nsplit,
                   const float* partial, const float* gamma, const float* beta, float eps, int act, void* out,
                   cudaStream_t stream);
+int b200_gn_apply_stats(const void* x1, int C1, const float* st1, int T1, const void* x2, int C2, const float* st2,
+                        int T2, int dtype, int B, int HW, int G, int nsplit, const float* gamma, const float* beta,
+                        float eps, int act, void* out, cudaStream_t stream);
 /* layout changes at the API boundary (NCHW fp32 <-> channels-last), incl. `2x-1` (ncsnpp.py:261) and `h/sigma` (:379) */
 int b200_nchw_to_nhwc(const float* x, void* out, int dtype, int B, int C, int H, int W, int Cp, float scale,
                       float shift, cudaStream_t stream);
@@ -116,13 +119,17 @@ int b200_conv2d_simt(const void* x1, int C1, const void* x2, int C2, const void*
 int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride, int out_mode);
 int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias, const float* temb,
                    int temb_stride, const void* res, float out_scale, void* out, int out_mode, const float* sample_mul,
-                   int B, int H, int W, int Cout, int ksize, cudaStream_t stream);
+                   float* stats, int B, int H, int W, int Cout, int ksize, cudaStream_t stream);
+/* `stats` (may be NULL): by-product for the GroupNorm that consumes `out` -- per (image, slot, channel) sum and sum of
+ * squares of the bf16 output, [B][slots][Cout][2] fp32 with slots = b200_conv2d_tc_stat_slots(B, H, W); consumed by
+ * b200_gn_apply_stats, so the separate statistics pass over the activation disappears. */
+int b200_conv2d_tc_stat_slots(int B, int H, int W);
 /* 3x3 stride-2 VALID conv (zero beyond the input extent) on the same tensor-core kernel (TMA element strides):
  * F.conv2d(stride=2) of conv_downsample_2d (models/up_or_down_sampling.py:174-178) on the FIR-padded input, and
  * DDPM's pad(0,1,0,1)+conv3x3/2 (models/layers.py:596-608).  x [B,Hin,Win,C] bf16, out [B,Ho,Wo,Cout] bf16. */
 int b200_conv2d_tc_s2_supported(int C, int B, int Ho, int Wo, int Cout);
 int b200_conv2d_tc_s2(const void* x, int C, const void* w, const float* bias, const void* res, float out_scale,
-                      void* out, int B, int Hin, int Win, int Ho, int Wo, int Cout, cudaStream_t stream);
+                      void* out, float* stats, int B, int Hin, int Win, int Ho, int Wo, int Cout, cudaStream_t stream);
 /* softmax(q k^T scale) v per image on CUDA cores (models/layerspp.py:82-86); ld* = row strides in elements */
 int b200_attention_simt(const void* q, const void* k, const void* v, void* out, int dtype, int B, int L, int C,
                         int ldq, int ldk, int ldv, int ldo, float scale, cudaStream_t stream);

@@ -33,9 +33,12 @@ def _run(dev, B, H, W, C1, C2, Cout, k, with_bias=True, with_temb=True, with_res
     out = torch.full((B, H, W, Cout), float("nan"), device=dev, dtype=torch.bfloat16)
     lib = _lib.lib()
     assert lib.b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, k, 1, 0) == 1
+    T = lib.b200_conv2d_tc_stat_slots(B, H, W)
+    stats = torch.full((B, T, Cout, 2), float("nan"), device=dev)
+    stats_ptr = _lib.ptr(stats)
     rc = lib.b200_conv2d_tc(_lib.ptr(x1), C1, _lib.ptr(x2), C2, _lib.ptr(w), _lib.ptr(bias),
                             (temb.data_ptr() + 4 * 32) if with_temb else None, Cout + 64, _lib.ptr(res), scale,
-                            _lib.ptr(out), 0, None, B, H, W, Cout, k, _lib.stream())
+                            _lib.ptr(out), 0, None, stats_ptr, B, H, W, Cout, k, _lib.stream())
     _lib.check(rc, "b200_conv2d_tc")
     torch.cuda.synchronize()
     xx = torch.cat([x1, x2], -1) if C2 else x1
@@ -48,6 +51,11 @@ def _run(dev, B, H, W, C1, C2, Cout, k, with_bias=True, with_temb=True, with_res
     if with_res:
         ref = ref + res.float()
     ref = ref * scale
+    # statistics by-product: per-channel sum / sum of squares of the bf16 output, folded over the slots
+    st = stats.double().sum(1)
+    o = out.double().reshape(B, H * W, Cout)
+    assert torch.allclose(st[..., 0], o.sum(1), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(st[..., 1], (o * o).sum(1), rtol=1e-4, atol=1e-2)
     return out.float(), ref
 
 
@@ -115,7 +123,7 @@ def test_conv_tc_head_nchw(cuda, B, H, C, Cout, k):
     lib = _lib.lib()
     assert lib.b200_conv2d_tc_supported(C, 0, B, H, H, Cout, k, 1, 1) == 1
     _lib.check(lib.b200_conv2d_tc(_lib.ptr(x), C, None, 0, _lib.ptr(w), _lib.ptr(bias), None, 0, None, 1.0, _lib.ptr(out),
-                                  1, _lib.ptr(mul), B, H, H, Cout, k, _lib.stream()), "conv2d_tc head")
+                                  1, _lib.ptr(mul), None, B, H, H, Cout, k, _lib.stream()), "conv2d_tc head")
     torch.cuda.synchronize()
     ref = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), bias, padding=k // 2)
     ref = ref * mul[:, None, None, None]
@@ -137,7 +145,7 @@ def test_conv_tc_stride2(cuda, B, Hin, C, Cout, res):
     out = torch.full((B, Ho, Ho, Cout), float("nan"), device=cuda, dtype=torch.bfloat16)
     lib = _lib.lib()
     assert lib.b200_conv2d_tc_s2_supported(C, B, Ho, Ho, Cout) == 1
-    _lib.check(lib.b200_conv2d_tc_s2(_lib.ptr(x), C, _lib.ptr(w), _lib.ptr(bias), _lib.ptr(r), 0.5, _lib.ptr(out), B, Hin,
+    _lib.check(lib.b200_conv2d_tc_s2(_lib.ptr(x), C, _lib.ptr(w), _lib.ptr(bias), _lib.ptr(r), 0.5, _lib.ptr(out), None, B, Hin,
                                      Hin, Ho, Ho, Cout, _lib.stream()), "conv2d_tc_s2")
     torch.cuda.synchronize()
     xin = x.float().permute(0, 3, 1, 2)
