@@ -15,6 +15,8 @@ SHAPES = [  # B, H, W, C1, C2, Cout, k
     (1, 128, 128, 64, 0, 128, 3),    # one tile per image row
     (1, 16, 256, 64, 0, 128, 3),     # two tiles per image row
     (160, 16, 16, 256, 128, 256, 3),  # more tiles than SMs: persistent loop + both TMEM buffers
+    (83, 32, 32, 128, 128, 128, 3),   # Cout = 128 with many tiles: paired M tiles per CTA (MT = 2)
+    (1190, 8, 8, 128, 0, 128, 1),     # MT = 2 with an odd number of 2-image M tiles (last group half empty)
 ]
 
 
