@@ -242,6 +242,116 @@ __global__ void __launch_bounds__(256) upfirdn2d_nhwc4_kernel(const T* __restric
   }
 }
 
+// ---- fast planes kernels for the two resampling shapes of the score networks (4x4 filter, factor 2) ------------
+// No shared memory: every thread owns a small output block, issues all of its (vector) loads up front and keeps the
+// window in registers; halo overlap between neighbouring threads is served by L1.  HBM traffic = algorithmic.
+// down 2, pad0 = 1 (downsample_2d, models/up_or_down_sampling.py:227-257): 2 x 4 outputs from a 6 x 10 window.
+__global__ void __launch_bounds__(256) upfirdn2d_down2_kernel(const float* __restrict__ in, const float* __restrict__ k,
+                                                              float* __restrict__ out, long long total, int in_h,
+                                                              int in_w, int out_h, int out_w) {
+  float w[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) w[a][b] = __ldg(k + (3 - a) * 4 + (3 - b));
+  const int bw = out_w >> 2, bh = (out_h + 1) >> 1;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int tx = (int)(i % bw);
+    long long r = i / bw;
+    const int ty = (int)(r % bh);
+    const long long pl = r / bh;
+    const int ox0 = tx * 4, oy0 = ty * 2;
+    const float* ip = in + pl * (long long)in_h * in_w;
+    const int ix0 = ox0 * 2, iy0 = oy0 * 2 - 1;
+    float win[6][10];
+#pragma unroll
+    for (int y = 0; y < 6; ++y) {
+      const int iy = iy0 + y;
+      if (iy >= 0 && iy < in_h) {
+        const float* rp = ip + (long long)iy * in_w + ix0;
+        const float4 a = __ldg(reinterpret_cast<const float4*>(rp));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(rp + 4));
+        win[y][0] = ix0 > 0 ? __ldg(rp - 1) : 0.0f;
+        win[y][1] = a.x; win[y][2] = a.y; win[y][3] = a.z; win[y][4] = a.w;
+        win[y][5] = b.x; win[y][6] = b.y; win[y][7] = b.z; win[y][8] = b.w;
+        win[y][9] = ix0 + 8 < in_w ? __ldg(rp + 8) : 0.0f;
+      } else {
+#pragma unroll
+        for (int x = 0; x < 10; ++x) win[y][x] = 0.0f;
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      if (oy0 + a >= out_h) break;
+      float o[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        float acc = 0.0f;
+#pragma unroll
+        for (int ky = 0; ky < 4; ++ky)
+#pragma unroll
+          for (int kx = 0; kx < 4; ++kx) acc = fmaf(win[2 * a + ky][2 * c + kx], w[ky][kx], acc);
+        o[c] = acc;
+      }
+      *reinterpret_cast<float4*>(out + (pl * out_h + oy0 + a) * (long long)out_w + ox0) = make_float4(o[0], o[1], o[2], o[3]);
+    }
+  }
+}
+
+// up 2, pad0 = 2 (upsample_2d, models/up_or_down_sampling.py:195-224): 2 x 8 outputs from a 3 x 6 window.
+__global__ void __launch_bounds__(256) upfirdn2d_up2_kernel(const float* __restrict__ in, const float* __restrict__ k,
+                                                            float* __restrict__ out, long long total, int in_h, int in_w,
+                                                            int out_h, int out_w) {
+  float w[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) w[a][b] = __ldg(k + (3 - a) * 4 + (3 - b));
+  const int bw = in_w >> 2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int tx = (int)(i % bw);
+    long long r = i / bw;
+    const int j = (int)(r % in_h);                    // input row: produces output rows 2j, 2j+1
+    const long long pl = r / in_h;
+    const int i0 = tx * 4;
+    const float* ip = in + pl * (long long)in_h * in_w;
+    float win[3][6];
+#pragma unroll
+    for (int y = 0; y < 3; ++y) {
+      const int iy = j - 1 + y;
+      if (iy >= 0 && iy < in_h) {
+        const float* rp = ip + (long long)iy * in_w + i0;
+        const float4 a = __ldg(reinterpret_cast<const float4*>(rp));
+        win[y][0] = i0 > 0 ? __ldg(rp - 1) : 0.0f;
+        win[y][1] = a.x; win[y][2] = a.y; win[y][3] = a.z; win[y][4] = a.w;
+        win[y][5] = i0 + 4 < in_w ? __ldg(rp + 4) : 0.0f;
+      } else {
+#pragma unroll
+        for (int x = 0; x < 6; ++x) win[y][x] = 0.0f;
+      }
+    }
+    // out[2j+a][2i+c] = sum_{dy,dx in {0,1}} in[j-1+a+dy][i-1+c+dx] * w[2dy+a][2dx+c]
+#pragma unroll
+    for (int a = 0; a < 2; ++a) {
+      float o[8];
+#pragma unroll
+      for (int x = 0; x < 4; ++x)
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          float acc = 0.0f;
+#pragma unroll
+          for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx) acc = fmaf(win[a + dy][x + c + dx], w[2 * dy + a][2 * dx + c], acc);
+          o[2 * x + c] = acc;
+        }
+      float* op = out + (pl * out_h + 2 * j + a) * (long long)out_w + 2 * i0;
+      __stcs(reinterpret_cast<float4*>(op), make_float4(o[0], o[1], o[2], o[3]));        // written once, never re-read
+      __stcs(reinterpret_cast<float4*>(op + 4), make_float4(o[4], o[5], o[6], o[7]));
+    }
+  }
+}
+
 template <int UP, int DOWN>
 static int launch_tiled(const float* in, const float* k, float* out, int planes, int in_h, int in_w, int out_h,
                         int out_w, int pad_x0, int pad_y0, cudaStream_t st) {
@@ -287,6 +397,23 @@ extern "C" int b200_upfirdn2d_f32(const float* in, const float* k, float* out, i
   int out_w = (in_w * up_x + pad_x0 + pad_x1 - kw) / down_x + 1;
   if (out_h <= 0 || out_w <= 0) return B200_ERR_ARG;
   if (n_planes == 0) return B200_OK;
+  const bool al16 = ((((uintptr_t)in | (uintptr_t)out) & 15) == 0);
+  if (kh == 4 && kw == 4 && al16 && up_x == 1 && up_y == 1 && down_x == 2 && down_y == 2 && pad_x0 == 1 && pad_y0 == 1 &&
+      in_w % 4 == 0 && out_w % 4 == 0 && out_w * 2 == in_w) {
+    const long long total = (long long)n_planes * ((out_h + 1) / 2) * (out_w / 4);
+    long long want = (total + 255) / 256;
+    const int blocks = (int)(want < (long long)B200_NUM_SMS * 64 ? want : (long long)B200_NUM_SMS * 64);
+    upfirdn2d_down2_kernel<<<blocks, 256, 0, st>>>(in, k, out, total, in_h, in_w, out_h, out_w);
+    B200_RETURN_LAST();
+  }
+  if (kh == 4 && kw == 4 && al16 && up_x == 2 && up_y == 2 && down_x == 1 && down_y == 1 && pad_x0 == 2 && pad_y0 == 2 &&
+      in_w % 4 == 0 && out_w == 2 * in_w && out_h == 2 * in_h) {
+    const long long total = (long long)n_planes * in_h * (in_w / 4);
+    long long want = (total + 255) / 256;
+    const int blocks = (int)(want < (long long)B200_NUM_SMS * 64 ? want : (long long)B200_NUM_SMS * 64);
+    upfirdn2d_up2_kernel<<<blocks, 256, 0, st>>>(in, k, out, total, in_h, in_w, out_h, out_w);
+    B200_RETURN_LAST();
+  }
   if (kh == 4 && kw == 4 && up_x == up_y && down_x == down_y) {
     int rc = B200_ERR_UNSUPPORTED;
     if (up_x == 1 && down_x == 1) rc = launch_tiled<1, 1>(in, k, out, n_planes, in_h, in_w, out_h, out_w, pad_x0, pad_y0, st);
