@@ -263,7 +263,7 @@ __device__ __forceinline__ void ns_load_win_smem(float (&w)[5][8], const float* 
   }
 }
 
-__global__ void __launch_bounds__(NS_THREADS) ns_velocity4_kernel(float* __restrict__ out, const float* __restrict__ vel,
+__global__ void __launch_bounds__(NS_THREADS, 3) ns_velocity4_kernel(float* __restrict__ out, const float* __restrict__ vel,
                                                                   const float* __restrict__ pres, int nx, int ny,
                                                                   float dt, float dx) {
   __shared__ __align__(16) float su[NSV_W * NSV_H];
