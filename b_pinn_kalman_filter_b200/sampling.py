@@ -20,7 +20,7 @@ import math
 import numpy as np
 import torch
 
-from . import _lib, sde_lib
+from . import _lib, sde_lib, sharding
 from .models import utils as mutils
 from .models.utils import get_score_fn
 
@@ -297,7 +297,7 @@ def langevin_update(x, grad, alpha, snr, z=None, process_group=None):
                    "b200_langevin_norm_sums")
         if process_group is not None:
             import torch.distributed as dist
-            dist.all_reduce(sums, group=process_group)
+            sharding.allreduce_norm_sums(sums, process_group)
             total = B * dist.get_world_size(process_group)
         _lib.check(lib.b200_sde_update(_lib.ptr(xn), _lib.ptr(xm), _lib.ptr(g), _lib.ptr(z), _lib.ptr(al), None, None,
                                        None, 1, _lib.ptr(sums), 1.0 / total, float(snr), B, n_per, seed, off, 0, st),
@@ -394,7 +394,7 @@ class FusedPCLoop:
         self.lib = _lib.lib()
         self.pg = process_group
         self.total_batch = total_batch or self.B
-        self.elem_base = rank_offset * self.n_per
+        self.elem_base = sharding.philox_element_base(rank_offset, self.n_per)
         self.seed = _SEED[0] if seed is None else seed
         self.snr = float(snr)
         self.use_graph = use_graph and NOISE_FN is None and process_group is None
@@ -470,9 +470,7 @@ class FusedPCLoop:
                        "b200_sample_sumsq")
             _lib.check(lib.b200_langevin_norm_sums(_lib.ptr(self.sums), _lib.ptr(self.ss[0]), _lib.ptr(self.ss[1]), B,
                                                    st), "b200_langevin_norm_sums")
-            if self.pg is not None:
-                import torch.distributed as dist
-                dist.all_reduce(self.sums, group=self.pg)
+            sharding.allreduce_norm_sums(self.sums, self.pg)
             _lib.check(lib.b200_sde_update(_lib.ptr(self.x), _lib.ptr(self.x_mean), _lib.ptr(score), zp,
                                            _lib.ptr(self.corr[1]), None, None, _lib.ptr(self.step_dev), 1,
                                            _lib.ptr(self.sums), 1.0 / self.total_batch, self.snr, B, n_per, self.seed,
@@ -552,13 +550,15 @@ class FusedPCLoop:
 
 def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
                    n_steps=1, probability_flow=False, continuous=False,
-                   denoise=True, eps=1e-3, device='cuda', process_group=None, rank_offset=0, total_batch=None):
+                   denoise=True, eps=1e-3, device='cuda', process_group=None, rank_offset=0, total_batch=None,
+                   gather_output=False):
     """Create a Predictor-Corrector (PC) sampler (sampling.py:355-411).
 
     Beyond the reference's arguments: `process_group` / `rank_offset` / `total_batch` describe a batch-sharded run
     (one process per GPU): `shape[0]` is this rank's shard, `rank_offset` its first global sample index (decorrelates
     the Philox streams) and the Langevin batch-mean norms are all-reduced over the group so that the step size is the
-    one the unsharded batch would get (sampling.py:276-278).
+    one the unsharded batch would get (sampling.py:276-278).  `gather_output=True` returns the samples of the whole
+    group, concatenated in rank order, on every rank (the one data-path collective of the sharded run).
 
     Returns `pc_sampler(model) -> (samples, nfe)` with nfe = sde.N * (n_steps + 1) exactly as the reference reports
     it (sampling.py:409).
@@ -594,7 +594,10 @@ def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
                     x = loop.x_mean if denoise else loop.x
                     if loop.forwards_per_step == 0:
                         x = loop.x
-                    return inverse_scaler(x.clone()), sde.N * (n_steps + 1)
+                    x = x.clone()
+                    if gather_output:
+                        x = sharding.gather_samples(x, process_group, total_batch)
+                    return inverse_scaler(x), sde.N * (n_steps + 1)
             # generic path: user-defined predictor/corrector classes around the engine
             x = prior(dev)
             timesteps = torch.linspace(sde.T, eps, sde.N, device=dev)
@@ -603,7 +606,10 @@ def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
                 vec_t = torch.ones(shape[0], device=dev) * timesteps[i]
                 x, x_mean = corrector_update_fn(x, vec_t, model=model)
                 x, x_mean = predictor_update_fn(x, vec_t, model=model)
-            return inverse_scaler(x_mean if denoise else x), sde.N * (n_steps + 1)
+            x = x_mean if denoise else x
+            if gather_output:
+                x = sharding.gather_samples(x, process_group, total_batch)
+            return inverse_scaler(x), sde.N * (n_steps + 1)
 
     return pc_sampler
 

@@ -126,14 +126,6 @@ def test_pc_trajectory_bf16_within_stated_bound(cuda, name):
     assert cases.rel_l2(x, c["out"]) < BF16_TOL, cases.rel_l2(x, c["out"])
 
 
-def test_registry_contract():
-    from b_pinn_kalman_filter_b200 import sampling
-    assert sampling.get_predictor("reverse_diffusion").__name__ == "ReverseDiffusionPredictor"
-    assert sampling.get_corrector("langevin").__name__ == "LangevinCorrector"
-    with pytest.raises(ValueError):
-        sampling.register_predictor(name="euler_maruyama")(sampling.EulerMaruyamaPredictor)
-
-
 def test_graph_replay_equals_eager(cuda):
     """A PC step captured into a CUDA graph and replayed gives the same bits as eager launches (fused Philox noise:
     the device step counter selects the stream, so frozen kernel arguments still draw fresh noise)."""
