@@ -44,6 +44,8 @@ struct ConvTcParams {
   float out_scale;
   bf16* out;                    // [B, H, W, Cout]                        (EPI 0)
   float* out_nchw;              // [B, cout_true, H, W] fp32, * sample_mul[b]  (EPI 1: network head, ncsnpp.py:371-379)
+  int narrow;                   // EPI 1: 0 = NCHW head above; 8 = [B, H, W, 8] bf16 (+ res of the same layout), the
+                                // 3-channel image pyramids of progressive='output_skip' (ncsnpp.py:343-365)
   const float* sample_mul;
   int cout_true;
   // optional by-product for the consumer GroupNorm: per-(image, slot, channel) sum and sum of squares of the bf16
@@ -190,7 +192,26 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
         uint32_t r[16];
         tc_ld16(t_addr, r);
         tc_wait_ld();
-        if (valid && half == 0) {
+        if (valid && half == 0 && p.narrow == 8) {
+          const size_t px = (((size_t)b * p.H + h) * p.W + w) * 8;
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[j]) + (bs ? __ldg(bs + j) : 0.0f);
+          if (p.res) {
+            const uint4 rr = __ldg(reinterpret_cast<const uint4*>(p.res + px));
+            const __nv_bfloat162* hh = reinterpret_cast<const __nv_bfloat162*>(&rr);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float2 f = __bfloat1622float2(hh[i]);
+              v[2 * i] += f.x; v[2 * i + 1] += f.y;
+            }
+          }
+          uint4 t;
+          __nv_bfloat162* ho = reinterpret_cast<__nv_bfloat162*>(&t);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) ho[i] = __floats2bfloat162_rn(v[2 * i] * p.out_scale, v[2 * i + 1] * p.out_scale);
+          *reinterpret_cast<uint4*>(p.out + px) = t;
+        } else if (valid && half == 0) {
           const float mul = (p.sample_mul ? __ldg(p.sample_mul + b) : 1.0f) * p.out_scale;
           float* op = p.out_nchw + (((size_t)b * p.cout_true) * p.H + h) * p.W + w;
 #pragma unroll
@@ -463,7 +484,7 @@ extern "C" int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int
   int TW, TH, TB, tw, th;
   if (stride != 1 || (ksize != 1 && ksize != 3)) return 0;
   if (C1 <= 0 || C1 % TC_BK || C2 < 0 || C2 % TC_BK || Cout <= 0) return 0;
-  if (out_mode == 0 ? (Cout % 128 != 0) : (out_mode != 1 || Cout > 16)) return 0;
+  if (out_mode == 0 ? (Cout % 128 != 0) : out_mode == 1 ? (Cout > 16) : (out_mode != 2 || Cout != 8)) return 0;
   if (B <= 0 || !tile_box(B, H, W, TW, TH, TB, tw, th)) return 0;
   return 1;
 }
@@ -474,14 +495,15 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
                               int ksize, cudaStream_t st) {
   if (!x1 || !w || !out || (C2 > 0 && !x2)) return B200_ERR_ARG;
   if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1, out_mode)) return B200_ERR_UNSUPPORTED;
-  if (out_mode == 1 && (temb || res)) return B200_ERR_UNSUPPORTED;
+  if ((out_mode == 1 && (temb || res)) || (out_mode == 2 && temb)) return B200_ERR_UNSUPPORTED;
   ConvTcParams p;
   p.B = B; p.H = H; p.W = W; p.C1 = C1; p.C2 = C2; p.Cout = Cout; p.taps_w = ksize; p.pad = ksize / 2; p.stride = 1;
   tile_box(B, H, W, p.TW, p.TH, p.TB, p.tiles_w, p.tiles_h);
   p.num_m = p.TB > 1 ? (B + p.TB - 1) / p.TB : B * p.tiles_w * p.tiles_h;
-  int BN = out_mode == 1 ? 16 : ((Cout % 256 == 0) ? 256 : 128);
+  int BN = out_mode != 0 ? 16 : ((Cout % 256 == 0) ? 256 : 128);
   if (BN == 256 && p.num_m * (Cout / 256) < B200_NUM_SMS) BN = 128;   // small levels: more, narrower tiles
-  p.num_n = out_mode == 1 ? 1 : Cout / BN;
+  p.num_n = out_mode != 0 ? 1 : Cout / BN;
+  p.narrow = out_mode == 2 ? 8 : 0;
   p.bias = bias; p.temb = temb; p.temb_stride = temb_stride; p.res = (const bf16*)res; p.out_scale = out_scale;
   p.out = (bf16*)out; p.out_nchw = (float*)out; p.sample_mul = sample_mul; p.cout_true = Cout;
   p.stats = out_mode == 0 ? stats : nullptr; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h;
@@ -493,7 +515,7 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   else a2 = a1;
   rc = weight_map(&wm, w, Cout, Ktot, BN);          // rows beyond Cout are zero-filled by TMA (head: 3 of 16)
   if (rc) return rc;
-  if (out_mode == 1) return launch<16, 1>(a1, a2, wm, a1, p, st);
+  if (out_mode != 0) return launch<16, 1>(a1, a2, wm, a1, p, st);
   CUtensorMap om;
   rc = act_map(&om, out, B, H, W, Cout, p.TW, p.TH, p.TB);
   if (rc) return rc;
@@ -523,7 +545,7 @@ extern "C" int b200_conv2d_tc_s2(const void* x, int C, const void* w, const floa
   if (BN == 256 && p.num_m * (Cout / 256) < B200_NUM_SMS) BN = 128;
   p.num_n = Cout / BN;
   p.bias = bias; p.temb = nullptr; p.temb_stride = 0; p.res = (const bf16*)res; p.out_scale = out_scale;
-  p.out = (bf16*)out; p.out_nchw = nullptr; p.sample_mul = nullptr; p.cout_true = Cout;
+  p.out = (bf16*)out; p.out_nchw = nullptr; p.sample_mul = nullptr; p.cout_true = Cout; p.narrow = 0;
   p.stats = stats; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h;
   CUtensorMap a1, wm, om;
   int rc = act_map(&a1, x, B, Hin, Win, C, p.TW, p.TH, p.TB, 2);

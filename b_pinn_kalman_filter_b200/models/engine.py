@@ -444,6 +444,11 @@ class ScoreEngine:
             tc.emit_s2(b, x, w, bias, res, out_scale, out, self.conv_flops(b, x, x2, out, ksize))
             self.tc_convs += 1
             return
+        if (self.use_tc and stride == 1 and tuple(pad) == (ksize // 2, ksize // 2) and x2 is None and temb_ptr is None
+                and tc.narrow_supported(b, x, out, ksize)):
+            tc.emit_narrow(b, x, w, bias, res, out_scale, out, ksize, self.conv_flops(b, x, x2, out, ksize))
+            self.tc_convs += 1
+            return
         if self.use_tc and tc.conv_supported(b, x, x2, out, ksize, stride, tuple(pad)):
             tc.emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, self.conv_flops(b, x, x2, out, ksize))
             self.tc_convs += 1

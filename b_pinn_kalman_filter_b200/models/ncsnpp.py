@@ -48,8 +48,10 @@ def build_ncsnpp(b, config):
     # ---- input ----------------------------------------------------------------------------------------------
     x = net.input_image(channels, size, size, rescale=not config.data.centered)
     pyramid_in = x if progressive_input != "none" else None
-    if progressive_input == "residual":
-        pyramid_in = net.x_stem      # 64-wide on the tensor-core path so that the FIR conv-downsample runs there
+    if progressive_input in ("residual", "input_skip"):
+        # 64-wide on the tensor-core path: the FIR conv-downsample ('residual') and the Combine conv1x1 ('input_skip')
+        # then run on tcgen05 with K = 64 (61 zero lanes) instead of on CUDA cores with K = 3
+        pyramid_in = net.x_stem
 
     hs = [net.conv3x3(net.x_stem, net.next_module(), nf)]
     hs_c = [nf]

@@ -43,6 +43,17 @@ def emit_head(b, x, w, bias, out_scale, out_ptr, sample_mul_ptr, cout, ksize, fl
            sample_mul_ptr, None, b.B, x.H, x.W, cout, ksize, flops=flops)
 
 
+def narrow_supported(b, x, out, ksize):
+    """3-channel image pyramid stored 8 wide (out_mode 2 of b200_conv2d_tc)."""
+    return ENABLED and out.C == 8 and (out.H, out.W) == (x.H, x.W) and bool(
+        _lib.lib().b200_conv2d_tc_supported(x.C, 0, b.B, x.H, x.W, 8, ksize, 1, 2))
+
+
+def emit_narrow(b, x, w, bias, res, out_scale, out, ksize, flops):
+    b.emit("b200_conv2d_tc", x, x.C, None, 0, w.data_ptr(), bias.data_ptr(), None, 0, res, out_scale, out, 2, None, None,
+           b.B, x.H, x.W, 8, ksize, flops=flops, tag="%dx%d %dx%d %d->8 pyramid" % (ksize, ksize, x.H, x.W, x.C))
+
+
 def attention_supported(L, C):
     return ENABLED and bool(_lib.lib().b200_attention_tc_supported(L, C))
 

@@ -115,7 +115,9 @@ int b200_conv2d_simt(const void* x1, int C1, const void* x2, int C2, const void*
  * C1 % 64 == C2 % 64 == 0, Cout % 128 == 0): TMA-fed implicit GEMM with TMEM accumulators, same fused epilogue.
  * w: packed [Cout][ksize*ksize*(C1+C2)] bf16.  b200_conv2d_tc_supported returns 1 when the shape is taken.
  * out_mode 0: channels-last bf16 [B,H,W,Cout].  out_mode 1 (network head, Cout <= 16): NCHW fp32 [B,Cout,H,W] scaled
- * by sample_mul[b] (`h / used_sigmas`, models/ncsnpp.py:377-379); w then has Cout rows. */
+ * by sample_mul[b] (`h / used_sigmas`, models/ncsnpp.py:377-379); w then has Cout rows.  out_mode 2 (Cout == 8 stored
+ * channels, the 3-channel image pyramids of progressive='output_skip', models/ncsnpp.py:343-365): channels-last bf16
+ * [B,H,W,8], out = (conv + bias + res) * out_scale with res of the same layout; w has 8 rows (unused ones zero). */
 int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize, int stride, int out_mode);
 int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias, const float* temb,
                    int temb_stride, const void* res, float out_scale, void* out, int out_mode, const float* sample_mul,

@@ -132,6 +132,38 @@ def test_conv_tc_head_nchw(cuda, B, H, C, Cout, k):
     assert (out - ref).abs().max().item() <= 1e-4 * max(1.0, ref.abs().max().item())
 
 
+@pytest.mark.parametrize("B,H,C,k,res", [(3, 32, 128, 3, True), (2, 64, 128, 3, False), (5, 8, 256, 3, True), (2, 256, 128, 3, True)])
+def test_conv_tc_narrow_pyramid(cuda, B, H, C, k, res):
+    """Image-pyramid conv of progressive='output_skip' (out_mode 2): 3 channels stored 8 wide, + residual pyramid."""
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import tc  # noqa: F401
+    g = torch.Generator(device="cpu").manual_seed(B + C + H)
+    x = torch.randn(B, H, H, C, generator=g).to(cuda, torch.bfloat16)
+    w = torch.zeros(8, k, k, C)
+    w[:3] = torch.randn(3, k, k, C, generator=g) / (k * k * C) ** 0.5
+    w = w.to(cuda, torch.bfloat16)
+    bias = torch.zeros(8)
+    bias[:3] = torch.randn(3, generator=g)
+    bias = bias.to(cuda)
+    r = torch.zeros(B, H, H, 8)
+    r[..., :3] = torch.randn(B, H, H, 3, generator=g)
+    r = r.to(cuda, torch.bfloat16)
+    out = torch.full((B, H, H, 8), float("nan"), device=cuda, dtype=torch.bfloat16)
+    lib = _lib.lib()
+    assert lib.b200_conv2d_tc_supported(C, 0, B, H, H, 8, k, 1, 2) == 1
+    _lib.check(lib.b200_conv2d_tc(_lib.ptr(x), C, None, 0, _lib.ptr(w), _lib.ptr(bias), None, 0, _lib.ptr(r) if res else None,
+                                  0.5, _lib.ptr(out), 2, None, None, B, H, H, 8, k, _lib.stream()), "conv2d_tc narrow")
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), bias, padding=k // 2)
+    ref = ref.permute(0, 2, 3, 1)
+    if res:
+        ref = ref + r.float()
+    ref = ref * 0.5
+    assert torch.isfinite(out.float()).all()
+    assert (out.float() - ref).abs().max().item() <= 1e-2 * max(1.0, ref.abs().max().item())   # bf16 output rounding
+    assert out[..., 3:].float().abs().max().item() == 0.0
+
+
 @pytest.mark.parametrize("B,Hin,C,Cout,res", [(3, 33, 64, 128, True), (5, 17, 128, 256, True), (9, 9, 256, 256, False),
                                               (2, 64, 128, 128, False)])
 def test_conv_tc_stride2(cuda, B, Hin, C, Cout, res):
