@@ -119,6 +119,8 @@ PC_CASES = {
     # (subVP + langevin/ald raises in the reference itself: subVPSDE has no `alphas`, sampling.py:269)
     "subvp_rd_none": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}, "subvpsde",
                       "reverse_diffusion", "none", 0.1, 1, True, 8),
+    # north_star's "fixed-seed 1000-step trajectory": the whole schedule, 2000 network evaluations
+    "ve_rd_langevin_1000": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 1000),
 }
 
 

@@ -39,6 +39,8 @@ PC_CASES = {
     "vp_em_none": (_POS, "vpsde", "euler_maruyama", "none", 0.16, 1, True, 10),
     "vp_ancestral_langevin_discrete": (dict(_POS, beta_max=5.0), "vpsde", "ancestral_sampling", "langevin", 0.2, 1, False, 10),
     "subvp_rd_none": (_POS, "subvpsde", "reverse_diffusion", "none", 0.1, 1, True, 8),
+    # the full-length trajectory north_star asks for: N = 1000 PC steps (2000 network evaluations), fixed noise
+    "ve_rd_langevin_1000": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 1000),
 }
 
 

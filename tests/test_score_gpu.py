@@ -108,7 +108,9 @@ def test_pc_trajectory_fp32_matches_reference(cuda, name):
     c = cases.pc_case(name)
     x, nfe = _run_pc(c, cuda, "fp32")
     assert nfe == c["nfe"]
-    assert cases.rel_l2(x, c["out"]) < 1e-4, cases.rel_l2(x, c["out"])
+    # ~10 steps: 1e-4; the full 1000-step schedule compounds 2000 fp32 forwards: 1e-3 (both far inside 2e-2)
+    tol = 1e-3 if c["N"] >= 1000 else 1e-4
+    assert cases.rel_l2(x, c["out"]) < tol, cases.rel_l2(x, c["out"])
 
 
 @pytest.mark.parametrize("name", ["ve_rd_langevin", "vp_em_none"])
