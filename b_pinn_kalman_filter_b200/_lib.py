@@ -34,6 +34,9 @@ _SIGNATURES = {
                         c_u64, c_u64, c_ll, c_vp],
     "b200_fill_normal": [c_vp, c_ll, c_float, c_u64, c_u64, c_ll, c_vp],
     "b200_step_advance": [c_vp, c_int, c_vp],
+    "b200_grid_sample_fwd": [c_int, c_vp, c_vp, c_vp] + [c_int] * 10 + [c_vp],
+    "b200_grid_sample_bwd": [c_int, c_vp, c_vp, c_vp, c_vp, c_vp] + [c_int] * 10 + [c_vp],
+    "b200_grid_sample_grad2": [c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp] + [c_int] * 10 + [c_vp],
 }
 _RESTYPES = {"b200_build_info": ctypes.c_char_p}
 

@@ -141,6 +141,24 @@ int b200_attention_simt(const void* q, const void* k, const void* v, void* out, 
 int b200_attention_tc_supported(int L, int C);
 int b200_attention_tc(const void* qkv, void* out, int B, int L, int C, float scale, cudaStream_t stream);
 
+/* ---- grid_sample (op/grid_sample.py:15-22; models/flownet.py:8-25 is the caller) --------------------------------------
+ * dim = 2: input [N,C,H,W], grid [N,Ho,Wo,2] (x,y in [-1,1]), out [N,C,Ho,Wo]; dim = 3: input [N,C,D,H,W],
+ * grid [N,Do,Ho,Wo,3] (x,y,z), out [N,C,Do,Ho,Wo] (pass D = Do = 1 for dim 2).  fp32, contiguous.  Bilinear/trilinear,
+ * padding_mode 0 = zeros, 1 = border (the two op/grid_sample.py:16 accepts), align_corners as in F.grid_sample.
+ * fwd   replaces F.grid_sample(mode='bilinear')                       (op/grid_sample.py:38-39, 107-108)
+ * bwd   replaces aten::grid_sampler_{2d,3d}_backward                  (op/grid_sample.py:54-60, 124-130);
+ *       g_in is ACCUMULATED into (caller zero-fills it); g_in or g_grid may be NULL (output_mask).
+ * grad2 replaces gridsample_grad2.grad2_{2d,3d}(g2_gin, g2_ggrid, g_out, input, grid, padding_mode, align_corners)
+ *       -> [gg_out, g_in, g_grid] (op/grid_sample.cpp:26-56, op/grid_sample_kernel.cu:27-533); g_in accumulated. */
+int b200_grid_sample_fwd(int dim, float* out, const float* in, const float* grid, int N, int C, int D, int H, int W,
+                         int Do, int Ho, int Wo, int padding_mode, int align_corners, cudaStream_t stream);
+int b200_grid_sample_bwd(int dim, float* g_in, float* g_grid, const float* g_out, const float* in, const float* grid,
+                         int N, int C, int D, int H, int W, int Do, int Ho, int Wo, int padding_mode, int align_corners,
+                         cudaStream_t stream);
+int b200_grid_sample_grad2(int dim, float* gg_out, float* g_in, float* g_grid, const float* g2_gin, const float* g2_ggrid,
+                           const float* g_out, const float* in, const float* grid, int N, int C, int D, int H, int W,
+                           int Do, int Ho, int Wo, int padding_mode, int align_corners, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

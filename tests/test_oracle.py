@@ -76,3 +76,26 @@ def test_ns_step_oracle_properties():
     assert np.isfinite(v).all() and np.isfinite(p).all() and np.isfinite(d).all()
     # bug-compat mode equals the per-sample semantics at B = 1 (op/ns_step.cpp:70-72 is only wrong for B > 1)
     np.testing.assert_array_equal(ns_step_ref.update_velocity(vel[:1], pres[:1], dt, dx, bug_compat=True), v[:1])
+
+
+# ---------------------------------------------------------------- grid_sample
+@pytest.mark.parametrize("dim", [2, 3])
+@pytest.mark.parametrize("padding_mode", ["zeros", "border"])
+@pytest.mark.parametrize("align_corners", [True, False])
+def test_grid_sample_restatement_matches_aten(dim, padding_mode, align_corners):
+    """The differentiable restatement the grad2 oracle differentiates twice equals ATen's grid_sample (the
+    reference's own forward / backward, op/grid_sample.py:38-39, 54-60) in value and first derivative."""
+    import torch
+    from oracle import grid_sample_ref as gs
+    inp, grid = gs.synthetic(dim, seed=dim * 10 + align_corners)
+    inp, grid = inp.double(), grid.double()
+    y_ref = gs.forward(inp, grid, padding_mode, align_corners)
+    y = gs.sample(inp, grid, padding_mode, align_corners)
+    torch.testing.assert_close(y, y_ref, rtol=1e-12, atol=1e-12)
+    go = torch.randn(y.shape, generator=torch.Generator().manual_seed(3)).double()
+    gi_ref, gg_ref = gs.backward(go, inp, grid, padding_mode, align_corners)
+    x = inp.clone().requires_grad_(True)
+    g = grid.clone().requires_grad_(True)
+    gi, gg = torch.autograd.grad(gs.sample(x, g, padding_mode, align_corners), (x, g), go)
+    torch.testing.assert_close(gi, gi_ref, rtol=1e-12, atol=1e-12)
+    torch.testing.assert_close(gg, gg_ref, rtol=1e-10, atol=1e-10)
