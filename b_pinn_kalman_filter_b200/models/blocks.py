@@ -104,6 +104,7 @@ class Net:
                    2.0 if rescale else 1.0, -1.0 if rescale else 0.0)
         else:
             self.x_stem = x
+        b.rec("input", x=x, x_stem=self.x_stem, channels=channels, scale=2.0 if rescale else 1.0)
         return x
 
     def output_conv3x3(self, a, idx, channels, init_scale):
@@ -116,6 +117,7 @@ class Net:
             return
         b.emit("b200_nhwc_to_nchw", pyramid, b.plan.out.data_ptr(), b.dt, b.B, channels, pyramid.H, pyramid.W,
                pyramid.C, b.sample_mul.data_ptr())
+        b.rec("out_nhwc", x=pyramid, channels=channels)
 
     def finish(self):
         pass
@@ -208,6 +210,8 @@ class Net:
         if not b.dry:
             w, bias = e.packed_qkv(p, C)
             e.emit_conv(b, hn, None, w, bias, None, None, 1.0, qkv, 1, 1, (0, 0), p + ".qkv")
+            b.rec("conv", x=hn, x2=None, out=qkv, w=w, ksize=1, stride=1, pad=(0, 0), res=None, out_scale=1.0,
+                  head=False, cout=3 * C)
         a = b.attention_core(qkv, C)
         scale = INV_SQRT2 if skip_rescale else 1.0
         return b.conv(a, p + ".NIN_3", C, 1, nin=True, init_scale=init_scale, res=x, out_scale=scale)

@@ -151,6 +151,13 @@ class Builder:
         self.temb_all = None   # [B, sum(out_ch)] fp32
         self.temb_stride = 0
         self.sample_mul = None
+        self.tape = [] if (not dry and getattr(engine, "grad_mode", False)) else None   # primitives, for backward.py
+
+    def rec(self, kind, **kw):
+        """Records a primitive for the input-gradient pass (models/backward.py); no-op outside grad plans."""
+        if self.tape is not None:
+            kw["kind"] = kind
+            self.tape.append(kw)
 
     # ---- parameters -------------------------------------------------------------------------------------------
     def param(self, key, shape, init):
@@ -226,11 +233,13 @@ class Builder:
             s2, t2 = tc.request_stats(self, x2) if x2 is not None else (None, 0)
             self.emit("b200_gn_apply_stats", x, x.C, s1, t1, p2, c2, s2, t2, self.dt, self.B, HW, groups, ns,
                       self.e.dev(key + ".weight"), self.e.dev(key + ".bias"), 1e-6, 1 if act else 0, out)
+            self.rec("gn", x=x, x2=x2, out=out, key=key, groups=groups, act=act)
             return out
         part = self.f32(self.B * ns * groups * 2)
         self.emit("b200_gn_partial", x, x.C, p2, c2, self.dt, self.B, HW, groups, ns, part.data_ptr())
         self.emit("b200_gn_apply", x, x.C, p2, c2, self.dt, self.B, HW, groups, ns, part.data_ptr(),
                   self.e.dev(key + ".weight"), self.e.dev(key + ".bias"), 1e-6, 1 if act else 0, out)
+        self.rec("gn", x=x, x2=x2, out=out, key=key, groups=groups, act=act)
         return out
 
     def conv(self, x, key, cout, ksize, x2=None, stride=1, pad=None, out_hw=None, temb_off=None, res=None,
@@ -261,6 +270,8 @@ class Builder:
         if temb_off is not None:
             temb_ptr = self.temb_all.data_ptr() + 4 * temb_off
         p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+        self.rec("conv", x=x, x2=x2, out=out, w=w, ksize=ksize, stride=stride, pad=tuple(pad), res=res,
+                 out_scale=out_scale, head=nchw_out is not None, cout=cout)
         if nchw_out is not None:
             from . import tc
             fl = 2 * self.B * Ho * Wo * cout * cin_true * ksize * ksize
@@ -289,12 +300,14 @@ class Builder:
         k = self.e.fir_kernel(up)
         self.emit("b200_upfirdn2d_nhwc", x, k.data_ptr(), out, self.dt, self.B, x.H, x.W, x.C, 4, 4, up, down,
                   pad[0], pad[1])
+        self.rec("upfirdn", x=x, out=out, up=up, down=down, pad=tuple(pad))
         return out
 
     def nearest_up2(self, x):
         out = self.new(x.H * 2, x.W * 2, x.C)
         if not self.dry:
             self.emit("b200_nearest_up2_nhwc", x, out, self.dt, self.B, x.H, x.W, x.C)
+            self.rec("nearest_up2", x=x, out=out)
         return out
 
     def attention_core(self, qkv, C):
@@ -305,6 +318,7 @@ class Builder:
         L = qkv.H * qkv.W
         es = 2 if self.dt == DT_BF16 else 4
         self.e.emit_attention(self, qkv, out, L, C, es)
+        self.rec("attention", qkv=qkv, out=out, L=L, C=C)
         return out
 
 
@@ -474,17 +488,63 @@ class ScoreEngine:
                3 * C, C, float(int(C) ** (-0.5)), flops=4 * b.B * L * L * C)
 
     # ---- plans ------------------------------------------------------------------------------------------------
-    def plan(self, B):
-        if B not in self.plans:
+    def plan(self, B, grad=False):
+        """The launch list for batch size B.  grad=True: forward (activations retained) followed by the input-gradient
+        pass (models/backward.py); `plan.n_fwd` splits the two."""
+        key = (B, "grad") if grad else B
+        if key not in self.plans:
             if not self.params:
                 raise RuntimeError("ScoreEngine has no weights; call load_state_dict / init_weights first")
             with torch.cuda.device(self.device):
                 self.spec()
-                b = Builder(self, B, dry=False)
-                self.net_builder(b, self.config)
-                b.finalize()
-                self.plans[B] = b.plan
-        return self.plans[B]
+                self.grad_mode = grad
+                try:
+                    b = Builder(self, B, dry=False)
+                    self.net_builder(b, self.config)
+                    b.plan.n_fwd = len(b.plan.ops)
+                    if grad:
+                        from . import backward
+                        backward.emit_backward(b)
+                    b.finalize()
+                finally:
+                    self.grad_mode = False
+                self.plans[key] = b.plan
+        return self.plans[key]
+
+    def forward_for_grad(self, x, labels):
+        """Forward pass that keeps every activation; returns the network output [B, C, H, W] fp32 (a view of the
+        plan's output buffer).  Follow with `input_grad(v)`."""
+        _lib.require_cuda(x, labels)
+        B = x.shape[0]
+        p = self.plan(B, grad=True)
+        with torch.cuda.device(self.device):
+            p.x_in.copy_(x)
+            p.labels.copy_(labels.to(torch.float32).reshape(B))
+            st = _lib.stream()
+            for fn, args, name in p.ops[:p.n_fwd]:
+                rc = fn(*args, st)
+                if rc != 0:
+                    _lib.check(rc, name)
+        self._grad_B = B
+        p.grad_ready = True
+        return p.out
+
+    def input_grad(self, v):
+        """J^T v: gradient w.r.t. the input image of <model(x, labels), v> for the x of the last forward_for_grad."""
+        _lib.require_cuda(v)
+        p = self.plans[(self._grad_B, "grad")]
+        if not getattr(p, "grad_ready", False):
+            # the backward half reuses the buffers of activations it has consumed (liveness-packed workspace)
+            raise RuntimeError("input_grad: one call per forward_for_grad (the pass consumes the retained activations)")
+        p.grad_ready = False
+        with torch.cuda.device(self.device):
+            torch.mul(v.to(torch.float32), p.sample_mul_t.view(-1, 1, 1, 1), out=p.cot_in)
+            st = _lib.stream()
+            for fn, args, name in p.ops[p.n_fwd:]:
+                rc = fn(*args, st)
+                if rc != 0:
+                    _lib.check(rc, name)
+            return p.grad_out * p.grad_scale
 
     def forward(self, x, labels, out=None):
         """x: [B, C, H, W] fp32 CUDA; labels: [B] (sigma for Fourier nets, timestep index/continuous otherwise)."""

@@ -194,6 +194,45 @@ def get_score_fn(sde, model, train=False, continuous=False):
     return score_fn
 
 
+def get_score_vjp_fn(sde, model, continuous=False):
+    """score_and_vjp(x, t) -> (score, vjp) with vjp(v) = J_score(x)^T v (gradient w.r.t. x of <score(x, t), v>).
+
+    The engine-side replacement of autograd through `get_score_fn`'s output (what DPS needs,
+    inverse/conditional_sampling.py:116-136): same label / scale conventions as get_score_fn above, the Jacobian
+    product comes from ScoreEngine.forward_for_grad + input_grad.  One vjp call per score evaluation."""
+    if not isinstance(model, ScoreModel):
+        raise TypeError("get_score_vjp_fn needs a ScoreModel (B200 engine)")
+    eng = model.engine
+
+    def run(x, labels, scale):
+        out = eng.forward_for_grad(x, labels)
+        score = out * scale[:, None, None, None]
+
+        def vjp(v):
+            return eng.input_grad(v * scale[:, None, None, None])
+        return score, vjp
+
+    if isinstance(sde, (sde_lib.VPSDE, sde_lib.subVPSDE)):
+        def score_and_vjp(x, t):
+            if continuous or isinstance(sde, sde_lib.subVPSDE):
+                labels = t * 999
+                std = sde.marginal_prob(torch.zeros_like(x), t)[1]
+            else:
+                labels = t * (sde.N - 1)
+                std = sde.sqrt_1m_alphas_cumprod.to(labels.device)[labels.long()]
+            return run(x, labels, -1.0 / std)
+    elif isinstance(sde, sde_lib.VESDE):
+        def score_and_vjp(x, t):
+            if continuous:
+                labels = sde.marginal_prob(torch.zeros_like(x), t)[1]
+            else:
+                labels = torch.round((sde.T - t) * (sde.N - 1)).long()
+            return run(x, labels, torch.ones_like(t))
+    else:
+        raise NotImplementedError(f"SDE class {sde.__class__.__name__} not yet supported.")
+    return score_and_vjp
+
+
 def to_flattened_numpy(x):
     return x.detach().cpu().numpy().reshape((-1,))
 

@@ -215,3 +215,47 @@ class VESDE(SDE):
         sigma = table[i]
         adjacent = torch.where(i == 0, torch.zeros_like(t), table[i - 1])
         return torch.zeros_like(x), torch.sqrt(sigma ** 2 - adjacent ** 2)
+
+
+class OBSVSDE(SDE):
+    """Observation process y_t of a hidden state following `state_sde` (reference sde_lib.py:122-133)."""
+
+    def __init__(self, N, y0, operator):
+        super().__init__(N)
+        self.y0 = y0
+        self.operator = operator
+
+
+class LOBSVSDE(OBSVSDE):
+    """Linear observation SDE (reference sde_lib.py:310-352): y_t = alpha(t) y_0 + beta(t) A z.  Only what the DPS
+    sampler reads: `state_sde`, `y0`, `operator`, `observe_sampling`."""
+
+    def __init__(self, state_sde, y0, operator):
+        super().__init__(state_sde.N, y0, operator)
+        self.state_sde = state_sde
+
+    @property
+    def T(self):
+        return 1
+
+    def observe_sampling(self, z, t):
+        alpha, beta = self.state_sde.marginal_coef(t)
+        return alpha[:, None, None] * self.y0 + beta[:, None, None] * self.operator(z, False)
+
+    def sde(self, x, t):
+        return self.state_sde.sde(x, t)
+
+    def coefficient(self, t):
+        return self.state_sde.coefficient(t)
+
+    def marginal_coef(self, t):
+        return self.state_sde.marginal_coef(t)
+
+    def marginal_prob(self, x, t):
+        return self.state_sde.marginal_prob(x, t)
+
+    def prior_sampling(self, shape):
+        return None
+
+    def prior_logp(self, z):
+        return None

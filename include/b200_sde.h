@@ -159,6 +159,30 @@ int b200_grid_sample_grad2(int dim, float* gg_out, float* g_in, float* g_grid, c
                            const float* g_out, const float* in, const float* grid, int N, int C, int D, int H, int W,
                            int Do, int Ho, int Wo, int padding_mode, int align_corners, cudaStream_t stream);
 
+/* ---- input gradient of the score network (DPS: inverse/conditional_sampling.py:116-136 takes
+ * torch.autograd.grad(logp, x_t) through x0_hat = x_t/mean + std^2 score(x_t), i.e. J_model^T v w.r.t. the image) ------
+ * Convolution backward-data = the forward convolution entry points on flipped / transposed weights (packed by the host
+ * layer); the remaining backward pieces are below.  No weight gradients. */
+/* GroupNorm(+SiLU) backward over one or two concatenated sources; part_fwd = b200_gn_partial of the same sources */
+int b200_gn_bwd_partial(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G, int nsplit,
+                        const float* part_fwd, const float* gamma, const float* beta, float eps, int act, const void* dy,
+                        float* part_bwd, cudaStream_t stream);
+int b200_gn_bwd_apply(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G, int nsplit,
+                      const float* part_fwd, const float* part_bwd, const float* gamma, const float* beta, float eps,
+                      int act, const void* dy, void* dx1, int acc1, void* dx2, int acc2, cudaStream_t stream);
+/* out = sa * a + sb * b (b may be NULL): residual branches and gradient accumulation */
+int b200_axpby(const void* a, float sa, const void* b, float sb, void* out, int dtype, long long n, cudaStream_t stream);
+/* adjoint of b200_nearest_up2_nhwc: dx [B,H,W,C] (+)= 2x2 block sums of dy [B,2H,2W,C] */
+int b200_nearest_up2_bwd_nhwc(const void* dy, void* dx, int dtype, int B, int H, int W, int C, int acc, cudaStream_t stream);
+/* out [B,Ho,Wo,C] = 0 except out[:, 2i+1, 2j+1] = dy[:, i, j]: makes the backward-data of a 3x3 stride-2 VALID
+ * convolution a 3x3 stride-1 "same" convolution with the flipped kernel (models/layers.py:596-608) */
+int b200_zero_stuff2_nhwc(const void* dy, void* out, int dtype, int B, int Hi, int Wi, int Ho, int Wo, int C,
+                          cudaStream_t stream);
+/* backward of softmax(q k^T scale) v (models/layers.py:566-570): qkv, dqkv [B,L,3C]; dout [B,L,C];
+ * scratch 2*B*L*L floats */
+int b200_attention_bwd(const void* qkv, const void* dout, void* dqkv, float* scratch, int dtype, int B, int L, int C,
+                       float scale, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

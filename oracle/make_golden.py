@@ -106,6 +106,30 @@ def gen_score(ns, name):
     print("score", name, "out rms", float(y.pow(2).mean().sqrt()))
 
 
+VJP_CASES = ["nc_ddpm_vp"]     # input-gradient (DPS, inverse/conditional_sampling.py:116-136) of the C1/C4 network
+
+
+def gen_vjp(ns, name):
+    """J^T v of the REFERENCE network w.r.t. its input by autograd: what torch.autograd.grad(logp, x_t) propagates
+    through the score model in cond_grad_fn (inverse/conditional_sampling.py:125-131)."""
+    our, refm, over, B = SCORE_CASES[name]
+    cfg, rcfg = tiny_pair(our, refm, over)
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    sd = weights.trained_like_state_dict(spec, cfg, seed=1234)
+    model = ns.mutils.create_model(rcfg)
+    model.load_state_dict({"module." + k: v for k, v in sd.items()})
+    model.eval()
+    g = torch.Generator().manual_seed(99)
+    S, C = cfg.data.image_size, cfg.data.num_channels
+    x = (torch.rand(B, C, S, S, generator=g) * 1.5 - 0.25).requires_grad_(True)
+    lab = labels_for(cfg, B)
+    v = torch.randn(B, C, S, S, generator=torch.Generator().manual_seed(7))
+    y = model(x, lab)
+    gx, = torch.autograd.grad(y, x, v)
+    np.savez_compressed(os.path.join(GOLDEN, "vjp_%s.npz" % name), v=v.numpy(), gx=gx.numpy(), out=y.detach().numpy())
+    print("vjp", name, "gx rms", float(gx.pow(2).mean().sqrt()))
+
+
 PC_CASES = {
     # name: (overrides, sde, predictor, corrector, snr, n_steps, continuous, N)
     "ve_rd_langevin": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 12),
@@ -200,6 +224,9 @@ def main():
     for n in PC_CASES:
         if a.only in (None, "pc", n):
             gen_pc(ns, n)
+    for n in VJP_CASES:
+        if a.only in (None, "vjp", "vjp_" + n):
+            gen_vjp(ns, n)
 
 
 if __name__ == "__main__":

@@ -119,6 +119,17 @@ class RefScoreNet:
                 return self.ddpm(x, labels)
             return self.ncsnpp(x, labels)
 
+    def input_grad(self, x, labels, v):
+        """(out, J^T v): vector-Jacobian product w.r.t. the image by autograd through this restatement -- the quantity
+        DPS propagates through the score model (inverse/conditional_sampling.py:125-131).  DDPM path only: the
+        NCSN++ restatement resamples through the numpy FIR oracle, which autograd cannot see."""
+        if self.m.name != "ddpm":
+            raise NotImplementedError("input_grad oracle covers the DDPM network (configs C1 / C4)")
+        x = x.detach().cpu().to(self.dtype).requires_grad_(True)
+        out = self.ddpm(x, labels.detach().cpu())
+        gx, = torch.autograd.grad(out, x, v.detach().cpu().to(self.dtype))
+        return out.detach(), gx
+
     def ncsnpp(self, x, time_cond):
         m, nf = self.m, self.nf
         levels = len(m.ch_mult)

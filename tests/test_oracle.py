@@ -99,3 +99,15 @@ def test_grid_sample_restatement_matches_aten(dim, padding_mode, align_corners):
     gi, gg = torch.autograd.grad(gs.sample(x, g, padding_mode, align_corners), (x, g), go)
     torch.testing.assert_close(gi, gi_ref, rtol=1e-12, atol=1e-12)
     torch.testing.assert_close(gg, gg_ref, rtol=1e-10, atol=1e-10)
+
+
+# ---------------------------------------------------------------- input gradient (DPS)
+def test_oracle_input_grad_matches_reference_autograd():
+    """J^T v of the oracle DDPM equals the golden vector made by autograd through the REFERENCE model
+    (oracle/make_golden.py gen_vjp; inverse/conditional_sampling.py:125-131 is the consumer)."""
+    cfg, sd, x, labels, out = cases.score_case("nc_ddpm_vp")
+    g = np.load(golden_path("vjp_nc_ddpm_vp.npz"))
+    net = score_net_ref.RefScoreNet(cfg, sd)
+    y, gx = net.input_grad(x, labels, torch.from_numpy(g["v"]))
+    assert cases.max_rel(y, torch.from_numpy(g["out"])) < 2e-5
+    assert cases.max_rel(gx, torch.from_numpy(g["gx"])) < 5e-5, cases.max_rel(gx, torch.from_numpy(g["gx"]))
