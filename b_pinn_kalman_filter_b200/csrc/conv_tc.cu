@@ -18,6 +18,7 @@
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected thread),
 // warps 2..9 = epilogue (tcgen05.ld -> bias/temb/residual/scale -> bf16 -> global).  Persistent: grid = min(tiles,
 // 148), static round-robin tile schedule.
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -54,7 +55,7 @@ struct ConvTcParams {
   int stat_slots;
 };
 
-template <int BN>
+template <int BN, bool HALO = false>
 struct TcSmem {
   static constexpr int A_BYTES = TC_BM * TC_BK * 2;            // 16 KB
   static constexpr int B_BYTES = BN * TC_BK * 2;               // 32 KB (BN = 256)
@@ -68,12 +69,37 @@ struct TcSmem {
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;           // barriers + tmem slot, + slack for 1024 B alignment
 };
 
-template <int BN, int EPI>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+// Halo variant (3x3, BN = 128, tile = 8 wide x 16 high pixels of one image).  With one TMA box per tap an N = 128 tile
+// re-fetches its activations 9 times and is bound by SM ingress (~38 B/clk of unique activation bytes measured,
+// profiles/r01_conv128_ncu.txt) instead of the tensor pipe.  Here each 64-channel K block loads THREE boxes
+// {64 c, 8 w, 18 h} (one per horizontal tap, rows h0-1 .. h0+16) and the vertical taps are descriptor offsets of
+// r * 8 pixels * 128 B = r * 1024 B into the same box -- still 1024-byte aligned, so the SW128 phase is unchanged.
+// Activation ingress drops from 9 x 16 KB to 3 x 18 KB per K block (x 3.4 instead of x 9).  Weights ride a separate
+// ring (one 16 KB box per tap) filled by their own producer warp.
+constexpr int HALO_TW = 8, HALO_TH = 16;
+template <int BN>
+struct TcSmem<BN, true> {
+  static constexpr int BOX_BYTES = (HALO_TH + 2) * HALO_TW * 128;      // 18 KB
+  static constexpr int A_BYTES = 3 * BOX_BYTES;                        // 54 KB per K block
+  static constexpr int B_BYTES = BN * TC_BK * 2;
+  static constexpr int STAGES = 2;                                     // activation stages
+  static constexpr int WSTAGES = 4;                                    // weight ring
+  static constexpr int W_OFF = STAGES * A_BYTES;
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr int OUT_OFF = W_OFF + WSTAGES * B_BYTES;
+  static constexpr int OUT_BYTES = TC_BM * 128 * 2;
+  static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+  static constexpr int STAGE_BYTES = 0;
+};
+
+template <int BN, int EPI, bool HALO = false>
+__global__ void __launch_bounds__(TC_THREADS + (HALO ? 32 : 0), 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapOut,
                const ConvTcParams p) {
-  using S = TcSmem<BN>;
+  using S = TcSmem<BN, HALO>;
+  constexpr int NWS = HALO ? 4 : 0;     // weight-ring stages (halo variant only)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar0 = base + S::BAR_OFF;
@@ -82,7 +108,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   auto empty_bar = [&](int s) { return bar0 + 8u * (S::STAGES + s); };
   auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * S::STAGES + a); };
   auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * S::STAGES + 2 + a); };
-  const uint32_t tmem_slot = bar0 + 8u * (2 * S::STAGES + 4);
+  auto wfull_bar = [&](int s) { return bar0 + 8u * (2 * S::STAGES + 4 + s); };
+  auto wempty_bar = [&](int s) { return bar0 + 8u * (2 * S::STAGES + 4 + NWS + s); };
+  const uint32_t tmem_slot = bar0 + 8u * (2 * S::STAGES + 4 + 2 * NWS);
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -95,6 +123,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   if (threadIdx.x == 0) {
     for (int s = 0; s < S::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 8); }
+    for (int w = 0; w < NWS; ++w) { mbar_init(wfull_bar(w), 1); mbar_init(wempty_bar(w), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA1) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
@@ -126,6 +155,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
         int mt, nt, b0, h0, w0;
         tile_coords(tile, mt, nt);
         m_origin(mt, b0, h0, w0);
+        if constexpr (HALO) {
+          // activations only: three column-shifted boxes with one halo row above and below per 64-channel block
+          for (int kb = 0; kb < kb_per_tap; ++kb) {
+            mbar_wait(empty_bar(stage), phase ^ 1);
+            const uint32_t sa = base + stage * S::A_BYTES;
+            mbar_expect_tx(full_bar(stage), S::A_BYTES);
+            const int c = kb * TC_BK;
+#pragma unroll
+            for (int sx = 0; sx < 3; ++sx) {
+              if (c < p.C1) tma_load_4d(sa + sx * S::BOX_BYTES, &mapA1, full_bar(stage), c, w0 + sx - 1, h0 - 1, b0);
+              else tma_load_4d(sa + sx * S::BOX_BYTES, &mapA2, full_bar(stage), c - p.C1, w0 + sx - 1, h0 - 1, b0);
+            }
+            if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
+          }
+        } else {
         for (int tap = 0; tap < taps; ++tap) {
           const int r = tap / p.taps_w, s = tap - r * p.taps_w;
           for (int kb = 0; kb < kb_per_tap; ++kb) {
@@ -139,6 +183,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
         }
+        }
+      }
+    }
+  } else if (HALO && warp == 10) {
+    // ================= weight producer (halo variant): one [BN x 64] box per (K block, tap) =================
+    if constexpr (HALO) {
+      if (lane == 0) {
+        int ws = 0; uint32_t wphase = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+          int mt, nt;
+          tile_coords(tile, mt, nt);
+          for (int kb = 0; kb < kb_per_tap; ++kb)
+            for (int tap = 0; tap < 9; ++tap) {
+              mbar_wait(wempty_bar(ws), wphase ^ 1);
+              mbar_expect_tx(wfull_bar(ws), S::B_BYTES);
+              tma_load_2d(base + S::W_OFF + ws * S::B_BYTES, &mapW, wfull_bar(ws), tap * Ctot + kb * TC_BK, nt * BN);
+              if (++ws == NWS) { ws = 0; wphase ^= 1; }
+            }
+        }
       }
     }
   } else if (warp == 1) {
@@ -148,10 +211,33 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
+      int ws = 0; uint32_t wphase = 0;          // weight ring (halo variant)
+      (void)ws; (void)wphase;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        if constexpr (HALO) {
+          for (int kb = 0; kb < kb_per_tap; ++kb) {
+            mbar_wait(full_bar(stage), phase);
+            tc_fence_after();
+            const uint32_t sa = base + stage * S::A_BYTES;
+            for (int tap = 0; tap < 9; ++tap) {
+              const int r = tap / 3, sx = tap - r * 3;
+              mbar_wait(wfull_bar(ws), wphase);
+              tc_fence_after();
+              const uint64_t da = make_sw128_desc(sa + sx * S::BOX_BYTES + r * (HALO_TW * 128));
+              const uint64_t db = make_sw128_desc(base + S::W_OFF + ws * S::B_BYTES);
+#pragma unroll
+              for (int k = 0; k < TC_BK / 16; ++k)
+                tc_mma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | tap | k) != 0 ? 1u : 0u);
+              tc_commit(wempty_bar(ws));
+              if (++ws == NWS) { ws = 0; wphase ^= 1; }
+            }
+            tc_commit(empty_bar(stage));
+            if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
+          }
+        } else {
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
@@ -165,11 +251,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           tc_commit(empty_bar(stage));
           if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
+        }
         tc_commit(tfull_bar(acc));
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
-  } else {
+  } else if (warp < 10) {
     // ================= epilogue warps (2..9): two per TMEM lane quadrant, each takes half of the columns ==========
     const int q = warp & 3;                        // TMEM lane quadrant this warp may read
     const int half = (warp - 2) >> 2;
@@ -424,19 +511,26 @@ bool tile_box(int B, int H, int W, int& TW, int& TH, int& TB, int& tiles_w, int&
   return TB <= 256;
 }
 
-template <int BN, int EPI>
+template <int BN, int EPI, bool HALO = false>
 int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
            const ConvTcParams& p, cudaStream_t st) {
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_tc_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmem<BN>::TOTAL);
+    attr_err = cudaFuncSetAttribute(conv_tc_kernel<BN, EPI, HALO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    TcSmem<BN, HALO>::TOTAL);
   });
   if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
-  conv_tc_kernel<BN, EPI><<<grid, TC_THREADS, TcSmem<BN>::TOTAL, st>>>(a1, a2, w, om, p);
+  conv_tc_kernel<BN, EPI, HALO><<<grid, TC_THREADS + (HALO ? 32 : 0), TcSmem<BN, HALO>::TOTAL, st>>>(a1, a2, w, om, p);
   B200_RETURN_LAST();
+}
+
+// halo variant on / off (B200_CONV_HALO=0 disables it: A/B measurements)
+bool halo_enabled() {
+  static const bool on = [] { const char* e = getenv("B200_CONV_HALO"); return !(e && e[0] == '0'); }();
+  return on;
 }
 
 }  // namespace
@@ -517,6 +611,19 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   if (rc) return rc;
   if (out_mode != 0) return launch<16, 1>(a1, a2, wm, a1, p, st);
   CUtensorMap om;
+  if (BN == 128 && ksize == 3 && p.TB == 1 && H % HALO_TH == 0 && W % HALO_TW == 0 && halo_enabled()) {
+    // N = 128 tiles are bound by activation ingress, not by the tensor pipe: 8 x 16 pixel tiles with halo reuse
+    p.TW = HALO_TW; p.TH = HALO_TH; p.tiles_w = W / HALO_TW; p.tiles_h = H / HALO_TH;
+    p.num_m = B * p.tiles_w * p.tiles_h;
+    p.stat_slots = 2 * p.tiles_w * p.tiles_h;
+    rc = act_map(&a1, x1, B, H, W, C1, HALO_TW, HALO_TH + 2, 1);
+    if (rc) return rc;
+    if (C2 > 0) { rc = act_map(&a2, x2, B, H, W, C2, HALO_TW, HALO_TH + 2, 1); if (rc) return rc; }
+    else a2 = a1;
+    rc = act_map(&om, out, B, H, W, Cout, HALO_TW, HALO_TH, 1);
+    if (rc) return rc;
+    return launch<128, 0, true>(a1, a2, wm, om, p, st);
+  }
   rc = act_map(&om, out, B, H, W, Cout, p.TW, p.TH, p.TB);
   if (rc) return rc;
   return BN == 256 ? launch<256, 0>(a1, a2, wm, om, p, st) : launch<128, 0>(a1, a2, wm, om, p, st);

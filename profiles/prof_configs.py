@@ -18,7 +18,7 @@ CASES = {
     "C1b": ("vp/cifar10_ncsnpp_continuous", 4, 1000),
 }
 dev = torch.device("cuda:0")
-for name in (sys.argv[1:] or list(CASES)):
+for name in [n for n in (sys.argv[1:] or list(CASES)) if n in CASES]:
     cfgname, B, fps = CASES[name]
     cfg = configs.get_config(cfgname)
     cfg.device = dev
@@ -52,3 +52,34 @@ for name in (sys.argv[1:] or list(CASES)):
         print("   %-28s x%-4d %8.3f ms %s" % (k, n, t, ("%7.1f TFLOP/s" % (f / t / 1e9)) if f else ""))
     del model, plan
     torch.cuda.empty_cache()
+
+# ---- C4: one DPS right-hand side = forward (activations kept) + input gradient, DDPM 64x64x1 --------------------
+if not sys.argv[1:] or "C4" in sys.argv[1:]:
+    cfg = configs.get_config("inverse/nc_ddpmpp_inpaint_dps")
+    cfg.device = dev
+    model = mutils.ScoreModel(cfg, device=dev, precision="bf16", init=False)
+    model.init_weights(42, zero_init_scale=1.0)
+    for B in (2, 16):
+        x = torch.randn(B, 1, 64, 64, device=dev)
+        lab = torch.rand(B, device=dev) * 900 + 5
+        v = torch.randn(B, 1, 64, 64, device=dev)
+        eng = model.engine
+        for _ in range(2):
+            eng.forward_for_grad(x, lab)
+            g = eng.input_grad(v)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(5):
+            eng.forward_for_grad(x, lab)
+            g = eng.input_grad(v)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 5
+        plan = eng.plan(B, grad=True)
+        print("== C4 DPS rhs  B=%d  fwd+input-grad %.3f ms  (%d + %d launches)  %.1f rhs-evals/s  finite=%s"
+              % (B, ms, plan.n_fwd, len(plan.ops) - plan.n_fwd, B / ms * 1e3, bool(torch.isfinite(g).all())))
+        eng.forward_for_grad(x, lab)
+        tab = plan.run_timed(_lib.stream())          # whole list (forward + backward) with per-launch events
+        for k, (n, t, f) in sorted(tab.items(), key=lambda kv: -kv[1][1])[:12]:
+            print("   %-28s x%-4d %8.3f ms %s" % (k, n, t, ("%7.1f TFLOP/s" % (f / t / 1e9)) if f else ""))
