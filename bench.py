@@ -232,7 +232,49 @@ def aux_measurements(dev, pk):
                       "cell_updates_per_s": cells / ms * 1e3, "achieved": 52 * cells / ms / 1e6, "peak": pk["hbm"],
                       "unit": "GB/s", "frac": 52 * cells / ms / 1e6 / pk["hbm"],
                       "algorithmic_bytes_per_cell": 52}
+    del vel, pres, dens
+    out["other_configs"] = other_config_measurements(dev, timeit)
     return out
+
+
+def other_config_measurements(dev, timeit):
+    """BASELINE.json's other configs through the same engine at their per-GPU batch of the 8-GPU split:
+    C5 CelebA-HQ-256 NCSN++ forward (B=8), C1 DDPM 64x64 forward (B=4), C4 DPS right-hand side = forward + input
+    gradient (B=16).  Device-resident timings, random-init weights; reported beside the headline, not as bench lines."""
+    import torch
+    from b_pinn_kalman_filter_b200 import _lib, configs
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    res = {}
+    for tag, name, B, fwd_per_sample in (("C5_celebahq256_ncsnpp_forward", "ve/celebahq_256_ncsnpp_continuous", 8, 4000),
+                                         ("C1_nc_ddpm_forward", "vp/nc_ddpmpp", 4, 2000)):
+        cfg = configs.get_config(name)
+        cfg.device = dev
+        m = mutils.ScoreModel(cfg, device=dev, precision="bf16", init=False)
+        m.init_weights(42, zero_init_scale=1.0)
+        S, C = cfg.data.image_size, cfg.data.num_channels
+        y = m(torch.randn(B, C, S, S, device=dev), torch.rand(B, device=dev) * 10 + 0.1)
+        plan = m.engine.plan(B)
+        ms = timeit(lambda: plan.run(_lib.stream()), iters=5)
+        res[tag] = {"batch": B, "ms_per_forward": ms, "tflops": plan.flops() / ms / 1e9, "launches": len(plan.ops),
+                    "samples_per_s_per_gpu": B / (ms * 1e-3 * fwd_per_sample), "finite": bool(torch.isfinite(y).all())}
+        del m, plan
+        torch.cuda.empty_cache()
+    cfg = configs.get_config("inverse/nc_ddpmpp_inpaint_dps")
+    cfg.device = dev
+    m = mutils.ScoreModel(cfg, device=dev, precision="bf16", init=False)
+    m.init_weights(42, zero_init_scale=1.0)
+    B = 16
+    x, lab, v = torch.randn(B, 1, 64, 64, device=dev), torch.rand(B, device=dev) * 900 + 5, torch.randn(B, 1, 64, 64, device=dev)
+
+    def rhs():
+        m.engine.forward_for_grad(x, lab)
+        return m.engine.input_grad(v)
+
+    ms = timeit(rhs, iters=5)
+    plan = m.engine.plan(B, grad=True)
+    res["C4_dps_rhs_forward_plus_input_grad"] = {"batch": B, "ms": ms, "rhs_evals_per_s": B / ms * 1e3,
+                                                 "launches": len(plan.ops), "finite": bool(torch.isfinite(rhs()).all())}
+    return res
 
 
 def run_b200(a):

@@ -184,6 +184,49 @@ def gen_pc(ns, name):
     print("pc", name, "out rms", float(x.pow(2).mean().sqrt()), "nfe", nfe)
 
 
+def gen_ctrl(ns, kind):
+    """Inpainting / colorisation with the REFERENCE's controllable_generation.py (:8-180) on the tiny VE network, the
+    same injected noise stream as gen_pc (prior, then per step: corrector, mix, predictor, mix)."""
+    import controllable_generation as cg          # reference module (sys.path set by ref_import.load)
+    cfg, rcfg = tiny_pair("test/tiny_ncsnpp", "configs.ve.cifar10_ncsnpp_continuous", {})
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    sd = weights.trained_like_state_dict(spec, cfg, seed=77)
+    model = ns.mutils.create_model(rcfg)
+    model.load_state_dict({"module." + k: v for k, v in sd.items()})
+    model.eval()
+    N = 8
+    rcfg.model.num_scales = N
+    sde, eps = ref_import.get_sde(ns, rcfg)
+    B = 2
+    shape = (B, cfg.data.num_channels, cfg.data.image_size, cfg.data.image_size)
+    g = torch.Generator().manual_seed(21)
+    data = torch.rand(shape, generator=g)
+    mask = torch.zeros(shape)
+    mask[:, :, :, : shape[3] // 2] = 1.0
+    gray = data.mean(dim=1, keepdim=True).repeat(1, 3, 1, 1)
+    stream = noise_stream(999, shape)
+    torch_randn_like = torch.randn_like
+    prior_orig = type(sde).prior_sampling
+    try:
+        torch.randn_like = lambda t, **kw: next(stream).to(t.dtype)
+        type(sde).prior_sampling = lambda self, shp: next(stream) * cfg.model.sigma_max
+        pred, corr = ns.sampling.get_predictor("reverse_diffusion"), ns.sampling.get_corrector("langevin")
+        if kind == "inpaint":
+            fn = cg.get_pc_inpainter(sde, pred, corr, lambda v: v, 0.16, n_steps=1, probability_flow=False,
+                                     continuous=True, denoise=True, eps=eps)
+            out = fn(model, data, mask)
+        else:
+            fn = cg.get_pc_colorizer(sde, pred, corr, lambda v: v, 0.16, n_steps=1, probability_flow=False,
+                                     continuous=True, denoise=True, eps=eps)
+            out = fn(model, gray)
+    finally:
+        torch.randn_like = torch_randn_like
+        type(sde).prior_sampling = prior_orig
+    np.savez_compressed(os.path.join(GOLDEN, "ctrl_%s.npz" % kind), out=out.numpy(), data=data.numpy(), mask=mask.numpy(),
+                        gray=gray.numpy(), N=N, eps=eps, weight_seed=77, noise_seed=999)
+    print("ctrl", kind, "out rms", float(out.pow(2).mean().sqrt()))
+
+
 def gen_ops(ns):
     g = torch.Generator().manual_seed(5)
     cases = {}
@@ -224,6 +267,9 @@ def main():
     for n in PC_CASES:
         if a.only in (None, "pc", n):
             gen_pc(ns, n)
+    for kind in ("inpaint", "colorize"):
+        if a.only in (None, "ctrl", "ctrl_" + kind):
+            gen_ctrl(ns, kind)
     for n in VJP_CASES:
         if a.only in (None, "vjp", "vjp_" + n):
             gen_vjp(ns, n)

@@ -117,3 +117,13 @@ def rel_l2(a, b):
 def max_rel(a, b):
     a, b = a.double(), b.double()
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def ctrl_case(kind):
+    """Inpainting / colorisation golden (reference controllable_generation.py run by oracle/make_golden.py gen_ctrl)."""
+    cfg = our_config("test/tiny_ncsnpp", {})
+    g = np.load(os.path.join(GOLDEN, "ctrl_%s.npz" % kind))
+    sd = state_dict_for(cfg, int(g["weight_seed"]))
+    t = lambda k: torch.from_numpy(g[k])
+    return dict(cfg=cfg, sd=sd, out=t("out"), data=t("data"), mask=t("mask"), gray=t("gray"), N=int(g["N"]),
+                eps=float(g["eps"]), noise_seed=int(g["noise_seed"]), shape=tuple(g["data"].shape))

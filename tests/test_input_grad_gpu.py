@@ -89,3 +89,25 @@ def test_dps_rhs_matches_oracle(cuda, precision, tol):
     assert err < tol, err
     # the conditional term is not negligible in this comparison
     assert float(ref_cond.abs().max()) > 1e-3 * float(ref_score.abs().max())
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("bf16", 3e-2)])
+def test_likelihood_rhs_matches_oracle(cuda, precision, tol):
+    """Drift + Hutchinson divergence of the likelihood ODE (likelihood.py:27-37, 61-69): one engine forward + one
+    input-gradient pass against autograd through the oracle."""
+    from oracle import likelihood_ref, sampling_ref, score_net_ref
+    from b_pinn_kalman_filter_b200 import likelihood, sde_lib
+    cfg, sd, _, _, _ = cases.score_case("nc_ddpm_vp")
+    shape = (2, 1, 64, 64)
+    gen = torch.Generator().manual_seed(5)
+    x = torch.randn(shape, generator=gen) * 0.8
+    t = torch.tensor([0.71, 0.12])
+    eps = torch.randint(0, 2, shape, generator=gen).float() * 2 - 1
+    net = score_net_ref.RefScoreNet(cfg, sd)
+    rsde = sampling_ref.RefSDE("vpsde", cfg.model.num_scales, cfg.model.beta_min, cfg.model.beta_max)
+    ref_drift, ref_div = likelihood_ref.drift_div(net, rsde, x, t, eps)
+    m = _model(cfg, sd, cuda, precision)
+    sde = sde_lib.VPSDE(cfg.model.beta_min, cfg.model.beta_max, cfg.model.num_scales)
+    drift, div = likelihood.get_drift_div_fn(sde)(m, x.to(cuda), t.to(cuda), eps.to(cuda))
+    assert cases.rel_l2(drift.cpu(), ref_drift) < tol
+    assert cases.rel_l2(div.cpu(), ref_div) < 5 * tol, (div.cpu(), ref_div)

@@ -111,3 +111,21 @@ def test_oracle_input_grad_matches_reference_autograd():
     y, gx = net.input_grad(x, labels, torch.from_numpy(g["v"]))
     assert cases.max_rel(y, torch.from_numpy(g["out"])) < 2e-5
     assert cases.max_rel(gx, torch.from_numpy(g["gx"])) < 5e-5, cases.max_rel(gx, torch.from_numpy(g["gx"]))
+
+
+# ---------------------------------------------------------------- controllable generation
+@pytest.mark.parametrize("kind", ["inpaint", "colorize"])
+def test_oracle_controllable_generation_matches_reference(kind):
+    from oracle import controllable_ref
+    c = cases.ctrl_case(kind)
+    net = score_net_ref.RefScoreNet(c["cfg"], c["sd"])
+    m = c["cfg"].model
+    sde = sampling_ref.RefSDE("vesde", c["N"], sigma_min=m.sigma_min, sigma_max=m.sigma_max)
+    noises = cases.noise_stream(c["noise_seed"], c["shape"])
+    if kind == "inpaint":
+        out = controllable_ref.pc_inpaint(sde, net, c["data"], c["mask"], "reverse_diffusion", "langevin", 0.16, 1, True,
+                                          noises, c["eps"])
+    else:
+        out = controllable_ref.pc_colorize(sde, net, c["gray"], "reverse_diffusion", "langevin", 0.16, 1, True, noises,
+                                           c["eps"])
+    assert cases.rel_l2(out, c["out"]) < 1e-4, cases.rel_l2(out, c["out"])
