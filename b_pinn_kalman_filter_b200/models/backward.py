@@ -46,10 +46,12 @@ class _Grads:
         return self.g[id(act)]
 
     def target(self, act):
-        """(gradient activation, accumulate?) for a new contribution to d(act)."""
+        """(gradient activation, accumulate?) for a new contribution to d(act).  Zero-padded 64-wide images (the
+        tensor-core stem input and its FIR pyramid) get an 8-wide gradient: only their first channels carry one."""
         if id(act) in self.g:
             return self.g[id(act)], 1
-        g = Act(None, act.B, act.H, act.W, act.C, act.Ct)
+        C = 8 if (act.Ct < act.C and act.C == 64) else act.C
+        g = Act(None, act.B, act.H, act.W, C, act.Ct)
         self.g[id(act)] = g
         return g, 0
 
@@ -129,17 +131,8 @@ def _conv_bwd(b, G, t):
     for src in (x, x2):
         if src is None:
             continue
-        if src.Ct < src.C and src.C == 64 and b.e.use_tc:
-            # the zero-padded 64-wide image (tensor-core stem): only its first channels carry a gradient -> 8 wide
-            g8 = G.g.get(("img", id(src)))
-            acc = 1
-            if g8 is None:
-                g8, acc = Act(None, src.B, src.H, src.W, 8, src.Ct), 0
-                G.g[("img", id(src))] = g8
-            _dgrad(b, gy, wf, k, off, src.Ct, scale, g8, acc)
-        else:
-            gx, acc = G.target(src)
-            _dgrad(b, gy, wf, k, off, src.C, scale, gx, acc)
+        gx, acc = G.target(src)
+        _dgrad(b, gy, wf, k, off, src.Ct if gx.C != src.C else src.C, scale, gx, acc)
         off += src.C
 
 
@@ -178,9 +171,9 @@ def _upfirdn_bwd(b, G, t):
     gx, acc = G.target(x)
     k = b.e.fir_kernel(up)      # forward kernel carries the up^2 gain; the adjoint uses the same taps
     if acc:
-        tmp = Act(None, x.B, x.H, x.W, x.C, x.Ct)
+        tmp = Act(None, x.B, x.H, x.W, gx.C, x.Ct)
         b.emit("b200_upfirdn2d_nhwc", gy, k.data_ptr(), tmp, b.dt, b.B, gy.H, gy.W, gy.C, 4, 4, down, up, gp0, gp1)
-        b.emit("b200_axpby", tmp, 1.0, gx, 1.0, gx, b.dt, x.B * x.H * x.W * x.C)
+        b.emit("b200_axpby", tmp, 1.0, gx, 1.0, gx, b.dt, x.B * x.H * x.W * gx.C)
     else:
         b.emit("b200_upfirdn2d_nhwc", gy, k.data_ptr(), gx, b.dt, b.B, gy.H, gy.W, gy.C, 4, 4, down, up, gp0, gp1)
 
@@ -212,19 +205,19 @@ def emit_backward(b):
         elif kind == "input":
             inp = t
         elif kind == "out_nhwc":
-            raise NotImplementedError("input gradient through progressive='output_skip' heads")
+            # progressive='output_skip' head: out = pyramid[..., :channels] * sample_mul (NCHW fp32); the cotangent is
+            # already multiplied by sample_mul (engine.input_grad)
+            x = t["x"]
+            plan.cot_in = torch.zeros(b.B, t["channels"], x.H, x.W, device=b.e.device, dtype=torch.float32)
+            gx, acc = G.target(x)
+            assert not acc
+            b.emit("b200_nchw_to_nhwc", plan.cot_in.data_ptr(), gx, b.dt, b.B, t["channels"], x.H, x.W, gx.C, 1.0, 0.0)
         else:
             raise NotImplementedError("backward of primitive %r" % kind)
     if inp is None:
         raise RuntimeError("the network recorded no input primitive")
     x, xs, ch = inp["x"], inp["x_stem"], inp["channels"]
-    srcs = []
-    if ("img", id(xs)) in G.g:
-        srcs.append(G.g[("img", id(xs))])
-    if xs.C == 8 and G.has(xs):
-        srcs.append(G.get(xs))
-    if x is not xs and G.has(x):
-        srcs.append(G.get(x))
+    srcs = [G.get(a) for a in ((xs,) if x is xs else (xs, x)) if G.has(a)]
     if not srcs:
         raise RuntimeError("no gradient reached the input image")
     g = srcs[0]

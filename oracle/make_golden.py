@@ -106,7 +106,7 @@ def gen_score(ns, name):
     print("score", name, "out rms", float(y.pow(2).mean().sqrt()))
 
 
-VJP_CASES = ["nc_ddpm_vp"]     # input-gradient (DPS, inverse/conditional_sampling.py:116-136) of the C1/C4 network
+VJP_CASES = ["nc_ddpm_vp", "tiny_fourier_residual", "tiny_output_skip", "tiny_positional_vp"]     # input-gradient (DPS, inverse/conditional_sampling.py:116-136) of the C1/C4 network
 
 
 def gen_vjp(ns, name):

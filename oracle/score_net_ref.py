@@ -20,6 +20,23 @@ def _fir(x, k, up=1, down=1, pad=(0, 0)):
     return torch.from_numpy(np.asarray(y)).to(dtype=x.dtype)
 
 
+def _fir_torch(x, k, up=1, down=1, pad=(0, 0)):
+    """The same upfirdn2d written with differentiable torch ops (zero insertion, pad / crop, correlation with the
+    flipped kernel, decimation: op/upfirdn2d.py:159-200) -- used only when the oracle must be differentiated."""
+    B, C, H, W = x.shape
+    k = torch.as_tensor(np.asarray(k), dtype=x.dtype)
+    kh, kw = k.shape
+    y = x.reshape(B * C, 1, H, 1, W, 1)
+    y = F.pad(y, [0, up - 1, 0, 0, 0, up - 1])
+    y = y.reshape(B * C, 1, H * up, W * up)
+    p0, p1 = pad
+    y = F.pad(y, [max(p0, 0), max(p1, 0), max(p0, 0), max(p1, 0)])
+    y = y[:, :, max(-p0, 0):y.shape[2] - max(-p1, 0), max(-p0, 0):y.shape[3] - max(-p1, 0)]
+    y = F.conv2d(y, torch.flip(k, [0, 1]).reshape(1, 1, kh, kw))
+    y = y[:, :, ::down, ::down]
+    return y.reshape(B, C, y.shape[2], y.shape[3])
+
+
 class RefScoreNet:
     def __init__(self, config, state_dict, dtype=torch.float32):
         self.cfg = config
@@ -54,15 +71,18 @@ class RefScoreNet:
         return F.linear(self.act(temb), self.p(idx, "Dense_0.weight"), self.p(idx, "Dense_0.bias"))[:, :, None, None]
 
     # -- FIR resampling (up_or_down_sampling.py:195-257, 144-178) --
+    def fir(self, x, k, **kw):
+        return _fir_torch(x, k, **kw) if getattr(self, "differentiable", False) else _fir(x, k, **kw)
+
     def up2(self, x):
-        return _fir(x, self.fir_k * 4, up=2, pad=(2, 1))
+        return self.fir(x, self.fir_k * 4, up=2, pad=(2, 1))
 
     def down2(self, x):
-        return _fir(x, self.fir_k, down=2, pad=(1, 1))
+        return self.fir(x, self.fir_k, down=2, pad=(1, 1))
 
     def conv_down(self, idx, x):
         w, b = self.p(idx, "Conv2d_0.weight"), self.p(idx, "Conv2d_0.bias")
-        y = _fir(x, self.fir_k, pad=(2, 2))
+        y = self.fir(x, self.fir_k, pad=(2, 2))
         return F.conv2d(y, w, stride=2, padding=0) + b.reshape(1, -1, 1, 1)
 
     # -- blocks --
@@ -121,12 +141,15 @@ class RefScoreNet:
 
     def input_grad(self, x, labels, v):
         """(out, J^T v): vector-Jacobian product w.r.t. the image by autograd through this restatement -- the quantity
-        DPS propagates through the score model (inverse/conditional_sampling.py:125-131).  DDPM path only: the
-        NCSN++ restatement resamples through the numpy FIR oracle, which autograd cannot see."""
-        if self.m.name != "ddpm":
-            raise NotImplementedError("input_grad oracle covers the DDPM network (configs C1 / C4)")
+        DPS propagates through the score model (inverse/conditional_sampling.py:125-131).  FIR resampling switches
+        to its differentiable torch form (_fir_torch) for the duration."""
         x = x.detach().cpu().to(self.dtype).requires_grad_(True)
-        out = self.ddpm(x, labels.detach().cpu())
+        self.differentiable = True
+        try:
+            lab = labels.detach().cpu()
+            out = self.ddpm(x, lab) if self.m.name == "ddpm" else self.ncsnpp(x, lab)
+        finally:
+            self.differentiable = False
         gx, = torch.autograd.grad(out, x, v.detach().cpu().to(self.dtype))
         return out.detach(), gx
 

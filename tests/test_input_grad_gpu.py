@@ -29,6 +29,21 @@ def test_ddpm_input_grad_matches_reference(cuda, precision, tol):
     assert err < tol, err
 
 
+@pytest.mark.parametrize("name", ["tiny_fourier_residual", "tiny_output_skip", "tiny_positional_vp"])
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("bf16", 3e-2)])
+def test_ncsnpp_input_grad_matches_reference(cuda, name, precision, tol):
+    """NCSN++ blocks: BigGAN resblocks with FIR up/down, FIR conv-downsample of the input pyramid ('residual'),
+    Combine conv1x1 ('input_skip') and the output pyramid ('output_skip')."""
+    cfg, sd, x, labels, out = cases.score_case(name)
+    g = np.load(golden_path("vjp_%s.npz" % name))
+    m = _model(cfg, sd, cuda, precision)
+    y = m.engine.forward_for_grad(x.to(cuda), labels.to(cuda)).clone()
+    gx = m.engine.input_grad(torch.from_numpy(g["v"]).to(cuda))
+    assert cases.rel_l2(y.cpu(), torch.from_numpy(g["out"])) < (2e-5 if precision == "fp32" else 2e-2)
+    err = cases.rel_l2(gx.cpu(), torch.from_numpy(g["gx"]))
+    assert err < tol, err
+
+
 def test_input_grad_is_linear_in_v_and_batch_independent(cuda):
     """Size-independent properties at the C4 batch (B = 16): linear in the cotangent; samples do not mix."""
     cfg, sd, x, labels, _ = cases.score_case("nc_ddpm_vp")

@@ -102,11 +102,12 @@ def test_grid_sample_restatement_matches_aten(dim, padding_mode, align_corners):
 
 
 # ---------------------------------------------------------------- input gradient (DPS)
-def test_oracle_input_grad_matches_reference_autograd():
-    """J^T v of the oracle DDPM equals the golden vector made by autograd through the REFERENCE model
+@pytest.mark.parametrize("name", ["nc_ddpm_vp", "tiny_fourier_residual", "tiny_output_skip", "tiny_positional_vp"])
+def test_oracle_input_grad_matches_reference_autograd(name):
+    """J^T v of the oracle networks equals the golden vectors made by autograd through the REFERENCE models
     (oracle/make_golden.py gen_vjp; inverse/conditional_sampling.py:125-131 is the consumer)."""
-    cfg, sd, x, labels, out = cases.score_case("nc_ddpm_vp")
-    g = np.load(golden_path("vjp_nc_ddpm_vp.npz"))
+    cfg, sd, x, labels, out = cases.score_case(name)
+    g = np.load(golden_path("vjp_%s.npz" % name))
     net = score_net_ref.RefScoreNet(cfg, sd)
     y, gx = net.input_grad(x, labels, torch.from_numpy(g["v"]))
     assert cases.max_rel(y, torch.from_numpy(g["out"])) < 2e-5
