@@ -1,5 +1,7 @@
 // Shared device/host helpers for the sm_100a kernels of the PC-sampling hot path.
 #pragma once
+#include <cstdlib>
+#include <utility>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
@@ -121,5 +123,33 @@ struct Philox {
 };
 
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+
+
+// ---- programmatic dependent launch ------------------------------------------------------------------------------------
+// A kernel launched through b200_launch_pdl may be scheduled while its predecessor in the stream is still draining
+// (its CTAs take SMs as the predecessor's CTAs exit) and must call b200_pdl_wait() before it touches anything the
+// predecessor wrote; everything before the wait (barrier init, TMEM allocation, descriptor prefetch, index math)
+// overlaps the predecessor's tail and the launch latency.  The wait is a no-op under a plain launch.
+// Off by default: measured on the C3 bench it changes nothing (64.0 vs 65.0 ms per PC step; the GPU sits at its power
+// cap, so filling the 2 us launch gaps is paid back in clocks -- DESIGN.md "experiments").  B200_PDL=1 turns it on.
+__device__ __forceinline__ void b200_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Lets the NEXT kernel's CTAs be scheduled as soon as every CTA of this grid has got here (they still wait for this
+// grid's completion at their own b200_pdl_wait): call it once the CTA holds all the resources it will ever take.
+__device__ __forceinline__ void b200_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+inline bool b200_pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("B200_PDL"); return e && e[0] == '1'; }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t b200_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                   Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = b200_pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 }  // namespace b200

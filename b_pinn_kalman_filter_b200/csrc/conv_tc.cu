@@ -136,6 +136,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  b200_pdl_wait();   // everything above overlapped the previous kernel's tail; its outputs are read from here on
+  b200_pdl_trigger();
 
   auto tile_coords = [&](int tile, int& mt, int& nt) { nt = tile % p.num_n; mt = tile / p.num_n; };
   auto m_origin = [&](int mt, int& b0, int& h0, int& w0) {
@@ -523,7 +525,9 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
   if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
-  conv_tc_kernel<BN, EPI, HALO><<<grid, TC_THREADS + (HALO ? 32 : 0), TcSmem<BN, HALO>::TOTAL, st>>>(a1, a2, w, om, p);
+  cudaError_t le = b200_launch_pdl(conv_tc_kernel<BN, EPI, HALO>, dim3(grid), dim3(TC_THREADS + (HALO ? 32 : 0)),
+                                   (size_t)TcSmem<BN, HALO>::TOTAL, st, a1, a2, w, om, p);
+  if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
 }
 

@@ -80,6 +80,8 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(GnArgs a) {
   const int C = a.C1 + a.C2, CV = C >> 3;
   const int b = blockIdx.x / a.nsplit, sp = blockIdx.x % a.nsplit;
   const int cpg = C / a.G;
+  b200_pdl_wait();
+  b200_pdl_trigger();
   double* chs = reinterpret_cast<double*>(sh + 2 * a.G);      // [C] sums, [C] sums of squares (stats path only)
   if (a.st1) {
     // fold the slots per channel with all threads (coalesced over channels), then the channels per group
@@ -214,9 +216,11 @@ extern "C" int b200_gn_apply(const void* x1, int C1, const void* x2, int C2, int
   const int C = C1 + C2, thr = gn_threads(C);
   if (G % 2) return B200_ERR_UNSUPPORTED;              // keeps the double scratch 8-byte aligned
   const size_t smem = 2 * G * sizeof(float) + 2 * C * sizeof(double);
-  if (dtype == B200_DT_F32) gn_apply_kernel<float><<<B * nsplit, thr, smem, st>>>(a);
-  else if (dtype == B200_DT_BF16) gn_apply_kernel<bf16><<<B * nsplit, thr, smem, st>>>(a);
+  cudaError_t le;
+  if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float>, dim3(B * nsplit), dim3(thr), smem, st, a);
+  else if (dtype == B200_DT_BF16) le = b200_launch_pdl(gn_apply_kernel<bf16>, dim3(B * nsplit), dim3(thr), smem, st, a);
   else return B200_ERR_ARG;
+  if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
 }
 
@@ -237,8 +241,10 @@ extern "C" int b200_gn_apply_stats(const void* x1, int C1, const float* st1, int
   const int C = C1 + C2, thr = gn_threads(C);
   if (G % 2) return B200_ERR_UNSUPPORTED;              // keeps the double scratch 8-byte aligned
   const size_t smem = 2 * G * sizeof(float) + 2 * C * sizeof(double);
-  if (dtype == B200_DT_F32) gn_apply_kernel<float><<<B * nsplit, thr, smem, st>>>(a);
-  else if (dtype == B200_DT_BF16) gn_apply_kernel<bf16><<<B * nsplit, thr, smem, st>>>(a);
+  cudaError_t le;
+  if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float>, dim3(B * nsplit), dim3(thr), smem, st, a);
+  else if (dtype == B200_DT_BF16) le = b200_launch_pdl(gn_apply_kernel<bf16>, dim3(B * nsplit), dim3(thr), smem, st, a);
   else return B200_ERR_ARG;
+  if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
 }
