@@ -179,45 +179,66 @@ __global__ void __launch_bounds__(256) upfirdn2d_nhwc_kernel(const T* __restrict
 // input vector of the (WIN x WIN) window is loaded once and scattered into the outputs it feeds, which cuts the loads
 // per output from 16 to 9 (down 2), 2.25 (up 2) and 6.25 (pad-only) and keeps the kernel on the HBM roofline instead
 // of the L1 one.
-template <typename T, int UP, int DOWN>
+// PAD0 is a template parameter: with even block origins the tap index of window row wy is PAD0 % UP + wy * UP, a
+// compile-time number, so every "does this tap exist" test folds away (the runtime-pad version spent 66 branches and
+// 2.25x the necessary FMAs per thread on them and ran at 25 % of HBM for the up-2 shape).
+// NA = output rows per thread (x 2 columns): 2 for the up-2 shape (3 x 3 window), 1 for down-2 / pad-only, whose
+// 6 x 6 / 5 x 5 windows for two rows cost > 140 registers once the taps are static.
+template <typename T, int UP, int DOWN, int PAD0, int NA>
 __global__ void __launch_bounds__(256) upfirdn2d_nhwc4_kernel(const T* __restrict__ in, const float* __restrict__ k,
                                                               T* __restrict__ out, long long total, int C8, int in_h,
-                                                              int in_w, int out_h, int out_w, int pad0) {
+                                                              int in_w, int out_h, int out_w, int pad0_rt) {
+  static_assert(UP == 1 || NA == 2, "odd block origins need UP == 1");
+  // PAD0 < 0: padding (and with it the tap pattern) is a runtime value -- measured faster for the 6 x 6 / 5 x 5
+  // windows of down-2 / pad-only (3.4 / 1.9 TB/s vs 2.0 / 1.1 with static taps, which cost 140+ registers)
+  const int pad0 = PAD0 >= 0 ? PAD0 : pad0_rt;
+  constexpr int K0 = PAD0 >= 0 ? PAD0 % UP : 0;
+  constexpr int WINY = ((NA - 1) * DOWN + 3) / UP + 1;
   constexpr int WIN = (DOWN + 3) / UP + 1;      // input rows/cols that can touch a 2-wide output block
   __shared__ float sk[16];
   if (threadIdx.x < 16) sk[threadIdx.x] = k[(3 - (threadIdx.x >> 2)) * 4 + (3 - (threadIdx.x & 3))];   // flipped taps
   __syncthreads();
-  const int bw = (out_w + 1) >> 1, bh = (out_h + 1) >> 1;
+  const int bw = (out_w + 1) >> 1, bh = (out_h + NA - 1) / NA;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int c8 = (int)(i % C8);
     long long r = i / C8;
     const int ox0 = (int)(r % bw) * 2; r /= bw;
-    const int oy0 = (int)(r % bh) * 2;
+    const int oy0 = (int)(r % bh) * NA;
     const long long b = r / bh;
     const T* ip = in + b * (long long)in_h * in_w * C8 * 8 + c8 * 8;
     const int uy0 = oy0 * DOWN - pad0, ux0 = ox0 * DOWN - pad0;       // upsampled-grid coordinate of tap (0, 0)
     const int iy0 = floor_div(uy0 + UP - 1, UP), ix0 = floor_div(ux0 + UP - 1, UP);
-    float acc[2][2][8];
+    float acc[NA][2][8];
 #pragma unroll
-    for (int a = 0; a < 2; ++a)
+    for (int a = 0; a < NA; ++a)
 #pragma unroll
       for (int c = 0; c < 2; ++c)
 #pragma unroll
         for (int j = 0; j < 8; ++j) acc[a][c][j] = 0.0f;
-#pragma unroll
-    for (int wy = 0; wy < WIN; ++wy) {
+    // NA == 1: rows stay a real loop (6 loads in flight, ~60 registers); fully unrolled the compiler hoists all 24
+    // loads and needs 146 registers.  NA == 2 (3 x 3 window) is small enough to unroll.
+#pragma unroll(NA == 1 ? 1 : WINY)
+    for (int wy = 0; wy < WINY; ++wy) {
       const int iy = iy0 + wy;
-      if (iy < 0 || iy >= in_h) continue;
-      const int ky_a = iy * UP - uy0;                                  // tap row for output row oy0 (+DOWN per row)
+      const bool row_ok = iy >= 0 && iy < in_h;
+      const int ky_a = PAD0 >= 0 ? K0 + wy * UP : iy * UP - uy0;       // tap row for output row oy0 (-DOWN per row)
+      // the whole window row is requested before any of it is used (no control flow between the loads): WIN
+      // independent 16/32-byte loads in flight per thread instead of one
+      float v[WIN][8];
 #pragma unroll
       for (int wx = 0; wx < WIN; ++wx) {
         const int ix = ix0 + wx;
-        if (ix < 0 || ix >= in_w) continue;
-        const int kx_a = ix * UP - ux0;
-        float v[8];
-        Vec8<T>::load(ip + ((long long)iy * in_w + ix) * C8 * 8, v);
+        if (row_ok && ix >= 0 && ix < in_w) Vec8<T>::load(ip + ((long long)iy * in_w + ix) * C8 * 8, v[wx]);
+        else {
 #pragma unroll
-        for (int a = 0; a < 2; ++a) {
+          for (int j = 0; j < 8; ++j) v[wx][j] = 0.0f;
+        }
+      }
+#pragma unroll
+      for (int wx = 0; wx < WIN; ++wx) {
+        const int kx_a = PAD0 >= 0 ? K0 + wx * UP : (ix0 + wx) * UP - ux0;
+#pragma unroll
+        for (int a = 0; a < NA; ++a) {
           const int ky = ky_a - a * DOWN;
           if ((unsigned)ky >= 4u) continue;
 #pragma unroll
@@ -226,13 +247,13 @@ __global__ void __launch_bounds__(256) upfirdn2d_nhwc4_kernel(const T* __restric
             if ((unsigned)kx >= 4u) continue;
             const float wk = sk[ky * 4 + kx];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[a][c][j] = fmaf(v[j], wk, acc[a][c][j]);
+            for (int j = 0; j < 8; ++j) acc[a][c][j] = fmaf(v[wx][j], wk, acc[a][c][j]);
           }
         }
       }
     }
 #pragma unroll
-    for (int a = 0; a < 2; ++a)
+    for (int a = 0; a < NA; ++a)
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         const int oy = oy0 + a, ox = ox0 + c;
@@ -436,15 +457,18 @@ extern "C" int b200_upfirdn2d_nhwc(const void* in, const float* k, void* out, in
   if (out_h <= 0 || out_w <= 0) return B200_ERR_ARG;
   long long total = (long long)batch * out_h * out_w * (channels / 8);
   if (total == 0) return B200_OK;
-  if (kh == 4 && kw == 4 && ((up == 1 && down <= 2) || (up == 2 && down == 1))) {
-    const long long tot4 = (long long)batch * ((out_h + 1) / 2) * ((out_w + 1) / 2) * (channels / 8);
+  const int mode = (kh == 4 && kw == 4) ? ((up == 2 && down == 1 && pad0 == 2) ? 1 : (up == 1 && down == 2) ? 2
+                                                        : (up == 1 && down == 1) ? 3 : 0) : 0;
+  if (mode) {
+    const int na = 2;
+    const long long tot4 = (long long)batch * ((out_h + na - 1) / na) * ((out_w + 1) / 2) * (channels / 8);
     long long w4 = (tot4 + 255) / 256;
     const int blk = (int)(w4 < (long long)B200_NUM_SMS * 32 ? w4 : (long long)B200_NUM_SMS * 32);
-#define B200_UFD4(T, U, D) upfirdn2d_nhwc4_kernel<T, U, D><<<blk, 256, 0, st>>>((const T*)in, k, (T*)out, tot4, channels / 8, in_h, in_w, out_h, out_w, pad0)
+#define B200_UFD4(T, U, D, P0, NA) upfirdn2d_nhwc4_kernel<T, U, D, P0, NA><<<blk, 256, 0, st>>>((const T*)in, k, (T*)out, tot4, channels / 8, in_h, in_w, out_h, out_w, pad0)
     if (dtype == B200_DT_F32) {
-      if (up == 2) B200_UFD4(float, 2, 1); else if (down == 2) B200_UFD4(float, 1, 2); else B200_UFD4(float, 1, 1);
+      if (mode == 1) B200_UFD4(float, 2, 1, 2, 2); else if (mode == 2) B200_UFD4(float, 1, 2, -1, 2); else B200_UFD4(float, 1, 1, -1, 2);
     } else if (dtype == B200_DT_BF16) {
-      if (up == 2) B200_UFD4(bf16, 2, 1); else if (down == 2) B200_UFD4(bf16, 1, 2); else B200_UFD4(bf16, 1, 1);
+      if (mode == 1) B200_UFD4(bf16, 2, 1, 2, 2); else if (mode == 2) B200_UFD4(bf16, 1, 2, -1, 2); else B200_UFD4(bf16, 1, 1, -1, 2);
     } else {
       return B200_ERR_ARG;
     }
