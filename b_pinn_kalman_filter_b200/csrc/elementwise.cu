@@ -7,17 +7,24 @@
 namespace b200 {
 
 // x: [B, C, H, W] fp32  ->  out: [B, H, W, Cp] T with out = x*scale + shift, channels c >= C zero-filled.
+// One thread = one 8-channel group of one pixel (a single 16 / 32-byte store; the padded groups are pure zero stores).
 template <typename T>
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, T* __restrict__ out, int B, int C, int HW, int Cp,
                                     float scale, float shift) {
-  const long long total = (long long)B * HW * Cp;
+  const int G = Cp >> 3;
+  const long long total = (long long)B * HW * G;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    int c = (int)(i % Cp);
-    long long r = i / Cp;
-    int p = (int)(r % HW);
-    long long b = r / HW;
-    float v = c < C ? fmaf(__ldg(x + (b * C + c) * HW + p), scale, shift) : 0.0f;
-    out[i] = from_f<T>(v);
+    const int g = (int)(i % G);
+    long long r = i / G;
+    const int p = (int)(r % HW);
+    const long long b = r / HW;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      v[j] = c < C ? fmaf(__ldg(x + (b * C + c) * HW + p), scale, shift) : 0.0f;
+    }
+    Vec8<T>::store(out + i * 8, v);
   }
 }
 
@@ -198,7 +205,8 @@ extern "C" int b200_nchw_to_nhwc(const float* x, void* out, int dtype, int B, in
                                  float shift, cudaStream_t st) {
   if (!x || !out || B < 0 || C <= 0 || Cp < C) return B200_ERR_ARG;
   if (B == 0) return B200_OK;
-  const long long total = (long long)B * H * W * Cp;
+  if (Cp % 8) return B200_ERR_ARG;
+  const long long total = (long long)B * H * W * (Cp / 8);
   if (dtype == B200_DT_F32) nchw_to_nhwc_kernel<float><<<grid_for(total), 256, 0, st>>>(x, (float*)out, B, C, H * W, Cp, scale, shift);
   else if (dtype == B200_DT_BF16) nchw_to_nhwc_kernel<bf16><<<grid_for(total), 256, 0, st>>>(x, (bf16*)out, B, C, H * W, Cp, scale, shift);
   else return B200_ERR_ARG;

@@ -54,11 +54,14 @@ class Net:
         plan.labels = torch.zeros(B, device=e.device, dtype=torch.float32)
         plan.step_ptr = None
         emb = b.f32(B * embed_dim)
-        t1 = b.f32(B * 4 * nf)
-        t2 = b.f32(B * 4 * nf)
+        # uniform-label plans (the fused PC loop: every sample of the batch sits at the same time step) run the
+        # embedding MLP and the batched Dense_0 projection on ONE row and broadcast it (temb_stride = 0)
+        Bt = 1 if getattr(e, "uniform_mode", False) else B
+        t1 = b.f32(Bt * 4 * nf)
+        t2 = b.f32(Bt * 4 * nf)
         total = e.dense_total
-        b.temb_all = b.f32(B * total)
-        b.temb_stride = total
+        b.temb_all = b.f32(Bt * total)
+        b.temb_stride = total if Bt == B else 0
         b.sample_mul = b.f32(B)
         sig = e.params.get("sigmas")
         b.emit("b200_temb_embed", plan.labels.data_ptr(), None, 0 if kind == "fourier" else 1,
@@ -67,12 +70,12 @@ class Net:
                b.sample_mul.data_ptr(), B)
         plan.temb_op_index = len(plan.ops) - 1
         b.emit("b200_linear_f32", emb.data_ptr(), e.dev(self.lin0 + ".weight"), e.dev(self.lin0 + ".bias"),
-               t1.data_ptr(), B, embed_dim, 4 * nf, 0, 0, flops=2 * B * embed_dim * 4 * nf)
+               t1.data_ptr(), Bt, embed_dim, 4 * nf, 0, 0, flops=2 * Bt * embed_dim * 4 * nf)
         b.emit("b200_linear_f32", t1.data_ptr(), e.dev(self.lin1 + ".weight"), e.dev(self.lin1 + ".bias"),
-               t2.data_ptr(), B, 4 * nf, 4 * nf, 1, 0, flops=2 * B * 16 * nf * nf)
+               t2.data_ptr(), Bt, 4 * nf, 4 * nf, 1, 0, flops=2 * Bt * 16 * nf * nf)
         wcat, bcat = e.packed_dense()
-        b.emit("b200_linear_f32", t2.data_ptr(), wcat.data_ptr(), bcat.data_ptr(), b.temb_all.data_ptr(), B, 4 * nf,
-               total, 1, 0, flops=2 * B * 4 * nf * total)
+        b.emit("b200_linear_f32", t2.data_ptr(), wcat.data_ptr(), bcat.data_ptr(), b.temb_all.data_ptr(), Bt, 4 * nf,
+               total, 1, 0, flops=2 * Bt * 4 * nf * total)
 
     def dense(self, prefix, out_ch):
         """Registers a block's Dense_0 and returns its column offset in the batched projection."""
@@ -95,15 +98,13 @@ class Net:
         plan = b.plan
         plan.x_in = torch.zeros(b.B, channels, H, W, device=b.e.device, dtype=torch.float32)
         plan.out = torch.zeros(b.B, channels, H, W, device=b.e.device, dtype=torch.float32)
-        b.emit("b200_nchw_to_nhwc", plan.x_in.data_ptr(), x, b.dt, b.B, channels, H, W, 8,
-               2.0 if rescale else 1.0, -1.0 if rescale else 0.0)
         if b.e.use_tc:
-            # tensor-core stem: the same image in a 64-channel (one 128-byte TMA row) zero-padded tensor
-            self.x_stem = b.new(H, W, 64, channels)
-            b.emit("b200_nchw_to_nhwc", plan.x_in.data_ptr(), self.x_stem, b.dt, b.B, channels, H, W, 64,
-                   2.0 if rescale else 1.0, -1.0 if rescale else 0.0)
-        else:
-            self.x_stem = x
+            # tensor-core path: the image lives in a 64-channel (one 128-byte TMA row) zero-padded tensor, which
+            # feeds the stem convolution and the input pyramids alike; the 8-wide form is never read
+            x = b.new(H, W, 64, channels)
+        b.emit("b200_nchw_to_nhwc", plan.x_in.data_ptr(), x, b.dt, b.B, channels, H, W, x.C,
+               2.0 if rescale else 1.0, -1.0 if rescale else 0.0)
+        self.x_stem = x
         b.rec("input", x=x, x_stem=self.x_stem, channels=channels, scale=2.0 if rescale else 1.0)
         return x
 

@@ -488,16 +488,18 @@ class ScoreEngine:
                3 * C, C, float(int(C) ** (-0.5)), flops=4 * b.B * L * L * C)
 
     # ---- plans ------------------------------------------------------------------------------------------------
-    def plan(self, B, grad=False):
+    def plan(self, B, grad=False, uniform=False):
         """The launch list for batch size B.  grad=True: forward (activations retained) followed by the input-gradient
-        pass (models/backward.py); `plan.n_fwd` splits the two."""
-        key = (B, "grad") if grad else B
+        pass (models/backward.py); `plan.n_fwd` splits the two.  uniform=True: every sample carries the same label
+        (the fused PC loop), so the time-embedding MLP runs on one row."""
+        key = (B, "grad") if grad else ((B, "uniform") if uniform else B)
         if key not in self.plans:
             if not self.params:
                 raise RuntimeError("ScoreEngine has no weights; call load_state_dict / init_weights first")
             with torch.cuda.device(self.device):
                 self.spec()
                 self.grad_mode = grad
+                self.uniform_mode = uniform and not grad
                 try:
                     b = Builder(self, B, dry=False)
                     self.net_builder(b, self.config)
@@ -508,6 +510,7 @@ class ScoreEngine:
                     b.finalize()
                 finally:
                     self.grad_mode = False
+                    self.uniform_mode = False
                 self.plans[key] = b.plan
         return self.plans[key]
 

@@ -427,7 +427,7 @@ class FusedPCLoop:
                              torch.sqrt(step * 2).to(torch.float32).contiguous())
         self.labels = labels.to(torch.float32).contiguous()
         self.step_dev = torch.zeros(1, device=dev, dtype=torch.int32)
-        self.plan = eng.plan(self.B)
+        self.plan = eng.plan(self.B, uniform=True)     # every sample of the batch is at the same time step
         # network launches with the label read from the table at *step
         ops = list(self.plan.ops)
         fn, args, name = ops[self.plan.temb_op_index]
