@@ -28,6 +28,10 @@ _SIGNATURES = {
     "b200_ns_velocity_nonadvect": [c_vp, c_vp, c_vp, c_int, c_int, c_int, c_float, c_float, c_vp],
     "b200_ns_update_velocity": [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_float, c_float, c_int, c_vp],
     "b200_ns_update_pressure": [c_vp, c_vp, c_vp, c_int, c_int, c_int, c_float, c_float, c_vp],
+    "b200_ns_step_fused": [c_vp] * 6 + [c_int, c_int, c_int, c_float, c_float, c_vp],
+    "b200_rk_stage": [c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_vp, ctypes.c_double, c_ll, c_vp],
+    "b200_rk_error": [c_vp, c_vp, c_vp, c_vp, c_ll, c_int, c_vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, c_ll,
+                      c_vp],
     "b200_sample_sumsq": [c_vp, c_vp, c_vp, c_vp, c_int, c_ll, c_u64, c_u64, c_ll, c_vp, c_vp],
     "b200_langevin_norm_sums": [c_vp, c_vp, c_vp, c_int, c_vp],
     "b200_sde_update": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_float, c_int, c_ll,

@@ -411,3 +411,14 @@ extern "C" int b200_ns_update_pressure(float* pres_out, const float* pres, const
   ns_pressure_kernel<<<ns_grid(B, H, W), NS_THREADS, 0, st>>>(pres_out, pres, vel, W, H, dt, dx);
   B200_RETURN_LAST();
 }
+
+extern "C" int b200_ns_step_fused(float* dens_out, float* vel_out, float* pres_out, const float* dens, const float* vel,
+                                  const float* pres, int B, int H, int W, float dt, float dx, cudaStream_t st) {
+  if (!dens_out || !vel_out || !pres_out || !dens) return B200_ERR_ARG;
+  if (dens_out == dens || vel_out == vel || pres_out == pres) return B200_ERR_ARG;
+  int rc = b200_ns_update_velocity(vel_out, vel, pres, nullptr, B, H, W, dt, dx, 0, st);
+  if (rc) return rc;
+  rc = b200_ns_update_pressure(pres_out, pres, vel_out, B, H, W, dt, dx, st);
+  if (rc) return rc;
+  return b200_ns_update_density(dens_out, dens, vel_out, B, H, W, dt, dx, st);
+}

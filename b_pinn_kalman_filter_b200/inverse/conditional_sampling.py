@@ -16,13 +16,26 @@ from ..models.utils import from_flattened_numpy, get_score_vjp_fn, to_flattened_
 
 
 def get_solver(config, ode_func, x0, t1, shape, eps):
-    """inverse/conditional_sampling.py:10-29."""
+    """inverse/conditional_sampling.py:10-29.  Two calling conventions:
+      * numpy x0 (the reference's): ode_func(t, ndarray) -> ndarray, scipy / host Euler loop as in the reference;
+      * CUDA tensor x0: ode_func(t, fp32 tensor [n]) -> fp32 tensor [n]; 'RK45' / 'RK23' run on ode.solve_ivp and 'fixed'
+        is an in-place device loop -- the state never leaves HBM."""
+    on_device = torch.is_tensor(x0)
     if config.inverse.solver in ['RK45', 'RK23']:
+        if on_device:
+            from .. import ode
+            solution = ode.solve_ivp(ode_func, (t1, eps), x0, rtol=1e-3, atol=1e-3, method=config.inverse.solver)
+            return solution.y_final.reshape(shape).to(config.device).type(torch.float32)
         solution = integrate.solve_ivp(ode_func, (t1, eps), x0, rtol=1e-3, atol=1e-3, method=config.inverse.solver)
         return torch.tensor(solution.y[:, -1]).reshape(shape).to(config.device).type(torch.float32)
     elif config.inverse.solver == 'fixed':
-        x = x0
         dt = -.00002  # inverse ODE
+        if on_device:
+            x = x0.detach().reshape(-1).to(torch.float32).clone()
+            for t in torch.linspace(t1, eps, 5000).tolist():
+                x.add_(ode_func(t, x), alpha=dt)
+            return x.reshape(shape).to(config.device)
+        x = x0
         for t in torch.linspace(t1, eps, 5000):
             x += ode_func(float(t), x) * dt
         return torch.tensor(x).reshape(shape).to(config.device).type(torch.float32)
@@ -73,15 +86,21 @@ def get_dps_sampler(config, obsv_sde, shape, eps=1e-3):
     observation = obsv_sde.y0 + torch.randn_like(obsv_sde.y0, device=device) * obsv_var ** .5
     _, _, _, rhs = get_dps_functions(obsv_sde, observation, obsv_var, shape)
 
-    def dps_sampler(model, z=None):
+    def dps_sampler(model, z=None, solver='device'):
         x = obsv_sde.state_sde.prior_sampling(shape).to(device) if z is None else z
+        solve = partial(get_solver, config=config, shape=shape, eps=eps)
+        if solver == 'device':
+            def ode_func(t, x):
+                vec_t = torch.ones(shape[0], device=x.device) * t
+                return rhs(model, x.reshape(shape), vec_t).reshape(-1)
+
+            return solve(ode_func=ode_func, x0=x.to(torch.float32), t1=obsv_sde.state_sde.T)
 
         def ode_func(t, x):
             x_hat = from_flattened_numpy(x, shape).to(device).type(torch.float32)
             vec_t = torch.ones(shape[0], device=device) * t
             return to_flattened_numpy(rhs(model, x_hat, vec_t))
 
-        solver = partial(get_solver, config=config, shape=shape, eps=eps)
-        return solver(ode_func=ode_func, x0=to_flattened_numpy(x), t1=obsv_sde.state_sde.T)
+        return solve(ode_func=ode_func, x0=to_flattened_numpy(x), t1=obsv_sde.state_sde.T)
 
     return dps_sampler

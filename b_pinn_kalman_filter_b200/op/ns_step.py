@@ -61,3 +61,23 @@ def update_pressure(pres, vel, dt, dx):
                                                 float(dx), _lib.stream())
     _lib.check(rc, "b200_ns_update_pressure")
     return out
+
+
+def step(dens, vel, pres, dt, dx, out=None):
+    """One simulator step velocity -> pressure -> density (pinn_kalman/simulator.py:55-57) through one C-ABI call.
+    `out` = (dens, vel, pres) buffers to write into (ping-pong for rollouts), else fresh tensors.
+    Returns (dens, vel, pres)."""
+    dens, vel, pres = _prep(dens, vel, pres)
+    B, H, W = _shape(dens, vel)
+    _shape(pres, vel)
+    if out is None:
+        out = (torch.empty_like(dens), torch.empty_like(vel), torch.empty_like(pres))
+    d1, v1, p1 = out
+    for o, i in ((d1, dens), (v1, vel), (p1, pres)):
+        if o.shape != i.shape or o.dtype != torch.float32 or not o.is_contiguous() or o.device != i.device:
+            raise RuntimeError("ns_step.step: output buffers must match the inputs (fp32, contiguous, same device)")
+    with torch.cuda.device(dens.device):
+        rc = _lib.lib().b200_ns_step_fused(_lib.ptr(d1), _lib.ptr(v1), _lib.ptr(p1), _lib.ptr(dens), _lib.ptr(vel),
+                                           _lib.ptr(pres), B, H, W, float(dt), float(dx), _lib.stream())
+    _lib.check(rc, "b200_ns_step_fused")
+    return d1, v1, p1

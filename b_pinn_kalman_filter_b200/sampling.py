@@ -615,27 +615,43 @@ def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
 
 
 def get_ode_sampler(sde, shape, inverse_scaler, denoise=False, rtol=1e-5, atol=1e-5, method='RK45', eps=1e-3,
-                    device='cuda'):
-    """Probability-flow ODE sampler (sampling.py:414-485): scipy drives, the engine evaluates the drift."""
-    from scipy import integrate
+                    device='cuda', solver='device'):
+    """Probability-flow ODE sampler (sampling.py:414-485).  solver='device' (RK45 / RK23): the adaptive integrator of
+    ode.py keeps the state in HBM and reproduces scipy's step control; solver='scipy' (and every other `method`):
+    scipy drives as in the reference, with a D2H + H2D of the state per evaluation."""
 
     def drift_fn(model, x, t):
         score_fn = get_score_fn(sde, model, train=False, continuous=True)
         return sde.reverse(score_fn, probability_flow=True).sde(x, t)[0]
 
+    on_device = solver == 'device' and method in ('RK45', 'RK23')
+    if solver not in ('device', 'scipy'):
+        raise ValueError("get_ode_sampler: solver must be 'device' or 'scipy' (got %r)" % (solver,))
+
     def ode_sampler(model, z=None):
         with torch.no_grad():
             dev = model.engine.device if isinstance(model, mutils.ScoreModel) else torch.device(device)
             x = sde.prior_sampling(shape).to(dev) if z is None else z
+            if on_device:
+                from . import ode
 
-            def ode_func(t, xf):
-                xt = mutils.from_flattened_numpy(xf, shape).to(dev).type(torch.float32)
-                vec_t = torch.ones(shape[0], device=dev) * t
-                return mutils.to_flattened_numpy(drift_fn(model, xt, vec_t))
+                def ode_func(t, xf):
+                    vec_t = torch.ones(shape[0], device=dev) * t
+                    return drift_fn(model, xf.reshape(shape), vec_t).reshape(-1)
 
-            sol = integrate.solve_ivp(ode_func, (sde.T, eps), mutils.to_flattened_numpy(x), rtol=rtol, atol=atol,
-                                      method=method)
-            x = torch.tensor(sol.y[:, -1]).reshape(shape).to(dev).type(torch.float32)
+                sol = ode.solve_ivp(ode_func, (sde.T, eps), x.to(torch.float32), rtol=rtol, atol=atol, method=method)
+                x = sol.y_final.reshape(shape).type(torch.float32)
+            else:
+                from scipy import integrate
+
+                def ode_func(t, xf):
+                    xt = mutils.from_flattened_numpy(xf, shape).to(dev).type(torch.float32)
+                    vec_t = torch.ones(shape[0], device=dev) * t
+                    return mutils.to_flattened_numpy(drift_fn(model, xt, vec_t))
+
+                sol = integrate.solve_ivp(ode_func, (sde.T, eps), mutils.to_flattened_numpy(x), rtol=rtol, atol=atol,
+                                          method=method)
+                x = torch.tensor(sol.y[:, -1]).reshape(shape).to(dev).type(torch.float32)
             if denoise:
                 score_fn = get_score_fn(sde, model, train=False, continuous=True)
                 vec_eps = torch.ones(x.shape[0], device=dev) * eps

@@ -56,6 +56,10 @@ int b200_ns_update_velocity(float* vel_out, const float* vel, const float* pres,
                             float dt, float dx, int bug_compat, cudaStream_t stream);
 int b200_ns_update_pressure(float* pres_out, const float* pres, const float* vel, int B, int H, int W, float dt,
                             float dx, cudaStream_t stream);
+/* one simulator step (pinn_kalman/simulator.py:55-57, ukf_utils.py:109-111): velocity -> pressure -> density into the
+ * caller's output buffers (must not alias the inputs); three launches on `stream`, no allocation */
+int b200_ns_step_fused(float* dens_out, float* vel_out, float* pres_out, const float* dens, const float* vel,
+                       const float* pres, int B, int H, int W, float dt, float dx, cudaStream_t stream);
 /* building blocks: v* = v - dt grad(p) (op/ns_step_kernel.cu:180-202) and CIP advection of an arbitrary plane set
  * (op/ns_step_kernel.cu:114-158); strides in elements. */
 int b200_ns_velocity_nonadvect(float* vstar, const float* vel, const float* pres, int B, int H, int W, float dt,
@@ -182,6 +186,20 @@ int b200_zero_stuff2_nhwc(const void* dy, void* out, int dtype, int B, int Hi, i
  * scratch 2*B*L*L floats */
 int b200_attention_bwd(const void* qkv, const void* dout, void* dqkv, float* scratch, int dtype, int B, int L, int C,
                        float scale, cudaStream_t stream);
+
+/* ---- adaptive Runge-Kutta on the device (replaces the scipy.integrate.solve_ivp round trips of
+ * sampling.py:459-473, likelihood.py:86-99, inverse/conditional_sampling.py:10-29: the state stays in HBM, only the
+ * 8-byte error norm crosses to the host per step).  y, y_out fp64 [n]; K fp32 stage derivatives, stage j at
+ * K + j*kstride; a_host / e_host: ns coefficients in HOST memory (passed to the kernel by value). */
+#define B200_RK_MAX_STAGES 7
+#define B200_RK_PARTIALS 1184
+/* x32_out (may be NULL) = fp32(y + h sum_j a[j] K[j]); y_out (may be NULL) = the same in fp64 */
+int b200_rk_stage(float* x32_out, double* y_out, const double* y, const float* K, long long kstride, int ns,
+                  const double* a_host, double h, long long n, cudaStream_t stream);
+/* partial[0..B200_RK_PARTIALS) = block sums of (h sum_j e[j] K[j] / (atol + rtol max(|y|,|y_new|)))^2 (unused slots 0);
+ * ns = 7 (RK45) or 4 (RK23).  error_norm = sqrt(sum(partial) / n) as scipy/integrate/_ivp/rk.py:108-109 */
+int b200_rk_error(double* partial, const double* y, const double* y_new, const float* K, long long kstride, int ns,
+                  const double* e_host, double h, double atol, double rtol, long long n, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -252,6 +252,44 @@ def gen_ops(ns):
     print("ops", len(cases))
 
 
+def gen_ode(ns):
+    """Reference get_ode_sampler (sampling.py:414-485) and get_likelihood_fn (likelihood.py:40-113) on the tiny VP
+    network: scipy RK45 drives the reference on the CPU; fixed latent / data / Rademacher probe."""
+    import importlib
+    ref_likelihood = importlib.import_module("likelihood")
+    over = {"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}
+    cfg, rcfg = tiny_pair("test/tiny_ncsnpp", "configs.ve.cifar10_ncsnpp_continuous", over)
+    for c in (cfg, rcfg):
+        c.training.sde = "vpsde"
+        c.training.continuous = True
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    sd = weights.trained_like_state_dict(spec, cfg, seed=77)
+    model = ns.mutils.create_model(rcfg)
+    model.load_state_dict({"module." + k: v for k, v in sd.items()})
+    model.eval()
+    sde, eps = ref_import.get_sde(ns, rcfg)
+    shape = (2, cfg.data.num_channels, cfg.data.image_size, cfg.data.image_size)
+    gen = torch.Generator().manual_seed(2468)
+    z = torch.randn(shape, generator=gen)
+    fn = ns.sampling.get_ode_sampler(sde, shape, lambda v: v, denoise=False, rtol=1e-4, atol=1e-4, method="RK45",
+                                     eps=eps, device="cpu")
+    x, nfe = fn(model, z=z.clone())
+    data = torch.rand(shape, generator=gen) * 2 - 1
+    probe = torch.randint(0, 2, shape, generator=gen).float() * 2 - 1
+    orig = torch.randint_like
+    try:
+        torch.randint_like = lambda t, **kw: (probe + 1) / 2
+        lfn = ref_likelihood.get_likelihood_fn(sde, lambda v: (v + 1.) / 2., hutchinson_type="Rademacher", rtol=1e-4,
+                                               atol=1e-4, method="RK45", eps=1e-5)
+        bpd, zl, lnfe = lfn(model, data.clone())
+    finally:
+        torch.randint_like = orig
+    np.savez_compressed(os.path.join(GOLDEN, "ode_tiny_vp.npz"), z=z.numpy(), out=x.numpy(), nfe=nfe, data=data.numpy(),
+                        probe=probe.numpy(), bpd=bpd.numpy(), latent=zl.numpy(), lnfe=lnfe, rtol=1e-4, atol=1e-4,
+                        weight_checksum=np.float64(weight_checksum(sd)), weight_seed=77)
+    print("ode out rms", float(x.pow(2).mean().sqrt()), "nfe", nfe, "| bpd", bpd.tolist(), "nfe", lnfe)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default=None)
@@ -273,6 +311,8 @@ def main():
     for n in VJP_CASES:
         if a.only in (None, "vjp", "vjp_" + n):
             gen_vjp(ns, n)
+    if a.only in (None, "ode"):
+        gen_ode(ns)
 
 
 if __name__ == "__main__":

@@ -1,0 +1,162 @@
+"""Device-resident adaptive Runge-Kutta (ode.py + csrc/ode.cu) against scipy.integrate.solve_ivp itself, and the ODE
+sampler / likelihood built on it against golden vectors made by the reference (sampling.py:414-485,
+likelihood.py:40-113; oracle/make_golden.py gen_ode)."""
+import numpy as np
+import pytest
+import torch
+from scipy import integrate
+
+import cases
+from conftest import golden_path
+
+pytestmark = pytest.mark.gpu
+
+
+def _tiny_vp(dev, precision):
+    from b_pinn_kalman_filter_b200 import sde_lib
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    cfg = cases.our_config("test/tiny_ncsnpp", cases._POS)
+    cfg.training.sde = "vpsde"
+    cfg.training.continuous = True
+    g = np.load(golden_path("ode_tiny_vp.npz"))
+    sd = cases.state_dict_for(cfg, int(g["weight_seed"]))
+    assert abs(cases.weight_checksum(sd) - float(g["weight_checksum"])) <= 1e-9 * float(g["weight_checksum"])
+    m = mutils.ScoreModel(cfg, device=dev, precision=precision, init=False)
+    m.load_state_dict(sd)
+    sde = sde_lib.VPSDE(cfg.model.beta_min, cfg.model.beta_max, cfg.model.num_scales)
+    return m, sde, g
+
+
+@pytest.mark.parametrize("method", ["RK45", "RK23"])
+@pytest.mark.parametrize("span", [(0.0, 3.0), (1.0, 1e-3)])
+def test_rk_steps_like_scipy(cuda, method, span):
+    """Same right-hand side (evaluated on the device in fp32 for both) -> same accepted steps, same nfev, same state."""
+    from b_pinn_kalman_filter_b200 import ode
+    n = 70001                                                    # ragged: not a multiple of the block size
+    gen = torch.Generator().manual_seed(1)
+    y0 = (torch.randn(n, generator=gen) * 2).to(cuda)
+    w = (torch.rand(n, generator=gen) * 3 + 0.5).to(cuda)
+
+    w = w.double()
+
+    def fun(t, x):
+        # evaluated in fp64 and rounded once: 1-ulp differences of the fp64 state (device fma vs numpy dot) then almost
+        # never reach the fp32 derivative (a rare rounding flip moves one element by 6e-8, the steps by ~1e-6)
+        x = x.double()
+        return (-w * x * (1.0 + float(np.sin(3 * t))) + 0.3 * torch.cos(2 * x + t)).float()
+
+    def fun_np(t, y):
+        return fun(t, torch.from_numpy(y).to(cuda).float()).cpu().numpy()
+
+    ref = integrate.solve_ivp(fun_np, span, y0.cpu().numpy(), method=method, rtol=1e-5, atol=1e-7)
+    got = ode.solve_ivp(fun, span, y0, method=method, rtol=1e-5, atol=1e-7)
+    assert got.status == 0 and ref.status == 0
+    assert got.nfev == ref.nfev
+    assert len(got.steps) == len(ref.t) - 1
+    np.testing.assert_allclose(np.cumsum(got.steps) + span[0], ref.t[1:], rtol=1e-4, atol=1e-7)
+    assert got.t == span[1]
+    np.testing.assert_allclose(got.y_final.cpu().numpy(), ref.y[:, -1], rtol=1e-4, atol=1e-6)
+
+
+def test_rk_edge_cases(cuda):
+    from b_pinn_kalman_filter_b200 import ode
+    y0 = torch.ones(5, device=cuda)
+    r = ode.solve_ivp(lambda t, x: -x, (0.5, 0.5), y0)          # empty interval: one evaluation, state unchanged
+    assert r.status == 0 and r.nfev == 1 and torch.equal(r.y_final, y0.double())
+    r = ode.solve_ivp(lambda t, x: torch.zeros_like(x), (0.0, 1.0), y0)     # zero derivative: error norm exactly 0
+    s = integrate.solve_ivp(lambda t, y: np.zeros_like(y), (0.0, 1.0), np.ones(5))
+    assert r.nfev == s.nfev and torch.equal(r.y_final, y0.double())
+    with pytest.raises(ValueError):
+        ode.solve_ivp(lambda t, x: -x, (0.0, 1.0), y0, method="LSODA")
+    with pytest.raises(RuntimeError):
+        ode.solve_ivp(lambda t, x: -x, (0.0, 1.0), torch.ones(5))           # CPU tensor: no fallback
+    with pytest.raises(FloatingPointError):
+        ode.solve_ivp(lambda t, x: x * float("nan"), (0.0, 1.0), y0)
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("bf16", 5e-2)])
+def test_ode_sampler_matches_reference(cuda, precision, tol):
+    from b_pinn_kalman_filter_b200 import sampling
+    m, sde, g = _tiny_vp(cuda, precision)
+    z = torch.from_numpy(g["z"]).to(cuda)
+    fn = sampling.get_ode_sampler(sde, z.shape, lambda v: v, denoise=False, rtol=float(g["rtol"]), atol=float(g["atol"]),
+                                  method="RK45", eps=1e-3, device=cuda)
+    x, nfe = fn(m, z=z.clone())
+    err = cases.rel_l2(x.cpu(), torch.from_numpy(g["out"]))
+    assert err < tol, err
+    if precision == "fp32":
+        assert abs(nfe - int(g["nfe"])) <= 12, (nfe, int(g["nfe"]))      # at most two step attempts apart
+        # the scipy-driven path of the same sampler agrees with the device integrator step for step
+        fs = sampling.get_ode_sampler(sde, z.shape, lambda v: v, denoise=False, rtol=float(g["rtol"]),
+                                      atol=float(g["atol"]), method="RK45", eps=1e-3, device=cuda, solver="scipy")
+        xs, nfes = fs(m, z=z.clone())
+        assert nfes == nfe
+        assert cases.rel_l2(x.cpu(), xs.cpu()) < 1e-5
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-3), ("bf16", 3e-2)])
+def test_likelihood_matches_reference(cuda, precision, tol):
+    """bits/dim against the reference.  The data -> latent flow of this random-weight network is chaotic (the reference
+    itself moves the latent by 3.3e-4 for a 1e-6 relative change of the data, bits/dim by 1e-6), so the latent is only
+    compared loosely; the integrator is pinned by the scipy-driven run of the same right-hand side below."""
+    from b_pinn_kalman_filter_b200 import likelihood
+    m, sde, g = _tiny_vp(cuda, precision)
+    data = torch.from_numpy(g["data"]).to(cuda)
+    probe = torch.from_numpy(g["probe"]).to(cuda)
+    kw = dict(hutchinson_type="Rademacher", rtol=float(g["rtol"]), atol=float(g["atol"]), method="RK45", eps=1e-5)
+    orig = torch.randint_like
+    try:
+        torch.randint_like = lambda t, **kw: (probe + 1) / 2
+        bpd, latent, nfe = likelihood.get_likelihood_fn(sde, lambda v: (v + 1.) / 2., **kw)(m, data.clone())
+        if precision == "fp32":
+            bs, ls, ns = likelihood.get_likelihood_fn(sde, lambda v: (v + 1.) / 2., solver="scipy", **kw)(m, data.clone())
+    finally:
+        torch.randint_like = orig
+    assert cases.rel_l2(bpd.cpu(), torch.from_numpy(g["bpd"])) < tol, (bpd.cpu(), g["bpd"])
+    assert cases.rel_l2(latent.cpu(), torch.from_numpy(g["latent"])) < 0.15
+    if precision == "fp32":
+        assert abs(nfe - int(g["lnfe"])) <= 60, (nfe, int(g["lnfe"]))
+        assert ns == nfe
+        assert cases.rel_l2(bpd.cpu(), bs.cpu()) < 1e-5
+        assert cases.rel_l2(latent.cpu(), ls.cpu()) < 1e-3
+
+
+def test_dps_sampler_device_solver_matches_scipy_driver(cuda):
+    """get_dps_sampler (inverse/conditional_sampling.py:100-165) on C4's network: the device-resident RK45 against the
+    reference's own arrangement (scipy driving, state through numpy) over the same right-hand side."""
+    from types import SimpleNamespace
+    from b_pinn_kalman_filter_b200 import sde_lib
+    from b_pinn_kalman_filter_b200.inverse import conditional_sampling as cs
+    from b_pinn_kalman_filter_b200.inverse.operators import InpaintOperator
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    cfg, sd, _, _, _ = cases.score_case("nc_ddpm_vp")
+    m = mutils.ScoreModel(cfg, device=cuda, precision="bf16", init=False)
+    m.load_state_dict(sd)
+    shape = (2, 1, 64, 64)
+    gen = torch.Generator().manual_seed(11)
+    mask = torch.zeros(shape)
+    mask[:, :, :, :32] = 1.0
+    truth = torch.rand(shape, generator=gen) * 2 - 1
+    z = torch.randn(shape, generator=gen).to(cuda)
+    op = InpaintOperator(mask.to(cuda))
+    state = sde_lib.VPSDE(cfg.model.beta_min, cfg.model.beta_max, cfg.model.num_scales)
+    obsv = sde_lib.LOBSVSDE(state, op(truth.to(cuda), keep_shape=False), op)
+    config = SimpleNamespace(device=cuda, inverse=SimpleNamespace(variance=0.1, solver="RK45", sampler="dps"))
+    torch.manual_seed(0)
+    sampler = cs.get_sampler(config, obsv, shape, eps=0.7)      # short interval: a few dozen RHS evaluations
+    xd = sampler(m, z=z.clone())
+    xs = sampler(m, z=z.clone(), solver="scipy")
+    assert xd.shape == shape and torch.isfinite(xd).all()
+    assert cases.rel_l2(xd.cpu(), xs.cpu()) < 1e-5
+
+
+def test_fixed_solver_device_matches_host_loop(cuda):
+    """'fixed' solver (5000 Euler steps, conditional_sampling.py:20-27): CUDA-tensor convention vs numpy convention."""
+    from types import SimpleNamespace
+    from b_pinn_kalman_filter_b200.inverse import conditional_sampling as cs
+    config = SimpleNamespace(device=cuda, inverse=SimpleNamespace(solver="fixed"))
+    x0 = torch.linspace(-1, 1, 64)
+    host = cs.get_solver(config, lambda t, x: (-x * t).astype(np.float32), x0.numpy().copy(), 1.0, (8, 8), 1e-3)
+    dev = cs.get_solver(config, lambda t, x: -x * t, x0.to(cuda), 1.0, (8, 8), 1e-3)
+    assert dev.shape == (8, 8) and dev.device.type == "cuda"
+    assert cases.max_rel(dev.cpu(), host.cpu()) < 1e-5
