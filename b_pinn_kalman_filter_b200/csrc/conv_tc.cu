@@ -83,7 +83,7 @@ struct TcSmem<BN, true> {
   static constexpr int A_BYTES = 3 * BOX_BYTES;                        // 54 KB per K block
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGES = 2;                                     // activation stages
-  static constexpr int WSTAGES = 4;                                    // weight ring
+  static constexpr int WSTAGES = 5;                                    // weight ring (5 x 16 KB: what fits beside 2 x 54 KB)
   static constexpr int W_OFF = STAGES * A_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int OUT_OFF = W_OFF + WSTAGES * B_BYTES;
@@ -97,9 +97,9 @@ template <int BN, int EPI, bool HALO = false>
 __global__ void __launch_bounds__(TC_THREADS + (HALO ? 32 : 0), 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapOut,
-               const ConvTcParams p) {
+               const __grid_constant__ CUtensorMap mapRes, const ConvTcParams p) {
   using S = TcSmem<BN, HALO>;
-  constexpr int NWS = HALO ? 4 : 0;     // weight-ring stages (halo variant only)
+  constexpr int NWS = HALO ? TcSmem<BN, true>::WSTAGES : 0;     // weight-ring stages (halo variant only)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar0 = base + S::BAR_OFF;
@@ -110,7 +110,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * S::STAGES + 2 + a); };
   auto wfull_bar = [&](int s) { return bar0 + 8u * (2 * S::STAGES + 4 + s); };
   auto wempty_bar = [&](int s) { return bar0 + 8u * (2 * S::STAGES + 4 + NWS + s); };
-  const uint32_t tmem_slot = bar0 + 8u * (2 * S::STAGES + 4 + 2 * NWS);
+  const uint32_t res_bar = bar0 + 8u * (2 * S::STAGES + 4 + 2 * NWS);      // residual tile landed in the staging buffer
+  const uint32_t tmem_slot = res_bar + 8u;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -124,6 +125,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     for (int s = 0; s < S::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 8); }
     for (int w = 0; w < NWS; ++w) { mbar_init(wfull_bar(w), 1); mbar_init(wempty_bar(w), 1); }
+    mbar_init(res_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA1) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
@@ -264,6 +266,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     const int half = (warp - 2) >> 2;
     const int m_local = q * 32 + lane;
     int acc = 0; uint32_t acc_phase = 0;
+    // Residual (skip connection, EPI 0): a thread-per-pixel-row read of `res` touches 32 different 128-byte lines per
+    // warp instruction and made the epilogue of conv_1 / NIN_3 / the 1x1 shortcuts the bottleneck of the kernel
+    // (profiles/r01f_conv_tc_roles.txt).  Instead the residual tile is fetched by TMA INTO the output staging buffer
+    // (same box, same SW128 layout) one pass ahead; each thread then reads the 16-byte units it is about to overwrite.
+    uint32_t res_phase = 0;
+    auto res_fetch = [&](int tile_, int pass_) {           // thread 64 only
+      int mt_, nt_, b0_, h0_, w0_;
+      tile_coords(tile_, mt_, nt_);
+      m_origin(mt_, b0_, h0_, w0_);
+      mbar_expect_tx(res_bar, 2 * TC_BM * 128);
+      tma_load_4d(base + S::OUT_OFF, &mapRes, res_bar, nt_ * BN + pass_ * 128, w0_, h0_, b0_);
+      tma_load_4d(base + S::OUT_OFF + TC_BM * 128, &mapRes, res_bar, nt_ * BN + pass_ * 128 + 64, w0_, h0_, b0_);
+    };
+    if constexpr (EPI == 0) {
+      if (p.res && threadIdx.x == 64 && (int)blockIdx.x < num_tiles) res_fetch(blockIdx.x, 0);
+    }
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int mt, nt, b0, h0, w0;
       tile_coords(tile, mt, nt);
@@ -271,7 +289,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       const int lw = m_local % p.TW, lh = (m_local / p.TW) % p.TH, lb = m_local / (p.TW * p.TH);
       const int b = b0 + lb, h = h0 + lh, w = w0 + lw;
       const bool valid = b < p.B;
-      const size_t row = (((size_t)b * p.H + h) * p.W + w) * (size_t)p.Cout + (size_t)nt * BN;
       const float* tb = (p.temb && valid) ? p.temb + (size_t)b * p.temb_stride + nt * BN : nullptr;
       const float* bs = p.bias ? p.bias + nt * BN : nullptr;
       mbar_wait(tfull_bar(acc), acc_phase);
@@ -313,24 +330,24 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 #pragma unroll 1
       for (int pass = 0; pass < BN / 128; ++pass) {
       const int cbeg = pass * 128 + half * CH;
-      if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-      asm volatile("bar.sync 1, 256;" ::: "memory");  // staging buffer free (the previous store has read it)
-      uint4 rv[4];
-      if (p.res && valid) {
-        const uint4* rp = reinterpret_cast<const uint4*>(p.res + row + cbeg);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) rv[j] = __ldg(rp + j);
+      if (p.res) {
+        mbar_wait(res_bar, res_phase);                 // staging buffer holds this pass's residual tile
+        res_phase ^= 1;
+      } else {
+        if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        asm volatile("bar.sync 1, 256;" ::: "memory");  // staging buffer free (the previous store has read it)
       }
 #pragma unroll 1
       for (int c0 = cbeg; c0 < cbeg + CH; c0 += 32) {
         uint32_t r[32];
         tc_ld32(t_addr + c0, r);
-        uint4 rn[4];                                     // residual of the NEXT chunk: in flight during this one
-        const bool more = c0 + 32 < cbeg + CH;
-        if (p.res && valid && more) {
-          const uint4* rp = reinterpret_cast<const uint4*>(p.res + row + c0 + 32);
+        // this thread's row of the [128 x 64] SW128 box of the 64-channel group: unit u of row r sits at u ^ (r & 7)
+        uint8_t* srow = smem_raw + (base - smem_u32(smem_raw)) + S::OUT_OFF + ((c0 >> 6) & 1) * (TC_BM * 128) + m_local * 128;
+        uint4 rv[4];
+        if (p.res) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) rn[j] = __ldg(rp + j);
+          for (int j = 0; j < 4; ++j)
+            rv[j] = *reinterpret_cast<const uint4*>(srow + (((((c0 & 63) >> 3) + j) ^ (m_local & 7)) << 4));
         }
         tc_wait_ld();
         if (valid) {
@@ -362,8 +379,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               }
             }
           }
-          // stage into the [128 x 64] SW128 box of this 64-channel group: 16-byte unit u of row r sits at u ^ (r & 7)
-          uint8_t* srow = smem_raw + (base - smem_u32(smem_raw)) + S::OUT_OFF + ((c0 >> 6) & 1) * (TC_BM * 128) + m_local * 128;
+          // stage into the box (over the residual units just read)
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 t;
@@ -374,10 +390,6 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             const int unit = ((c0 & 63) >> 3) + j;
             *reinterpret_cast<uint4*>(srow + ((unit ^ (m_local & 7)) << 4)) = t;
           }
-        }
-        if (more) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) rv[j] = rn[j];
         }
       }
       if (pass == BN / 128 - 1) {                      // last TMEM read of this tile done: hand the accumulator back
@@ -414,6 +426,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             float* sp = p.stats + (((size_t)bi * p.stat_slots + slot) * p.Cout + ch) * 2;
             sp[0] = s1; sp[1] = s2;
           }
+        }
+      }
+      if (p.res) {
+        // next pass's residual tile: once the store above has read the staging buffer and the column sums are done
+        const bool last_pass = pass == BN / 128 - 1;
+        const bool more = !last_pass || tile + (int)gridDim.x < num_tiles;
+        if (p.stats) asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (threadIdx.x == 64 && more) {
+          asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          if (last_pass) res_fetch(tile + gridDim.x, 0); else res_fetch(tile, pass + 1);
         }
       }
       }
@@ -516,6 +538,12 @@ bool tile_box(int B, int H, int W, int& TW, int& TH, int& TB, int& tiles_w, int&
 template <int BN, int EPI, bool HALO = false>
 int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
            const ConvTcParams& p, cudaStream_t st) {
+  // residual tiles are fetched with the geometry of the output boxes (same tensor shape, other base pointer)
+  CUtensorMap rm = om;
+  if (EPI == 0 && p.res) {
+    const int rc = act_map(&rm, p.res, p.B, p.H, p.W, p.Cout, p.TW, p.TH, p.TB);
+    if (rc) return rc;
+  }
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
@@ -526,7 +554,7 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
   cudaError_t le = b200_launch_pdl(conv_tc_kernel<BN, EPI, HALO>, dim3(grid), dim3(TC_THREADS + (HALO ? 32 : 0)),
-                                   (size_t)TcSmem<BN, HALO>::TOTAL, st, a1, a2, w, om, p);
+                                   (size_t)TcSmem<BN, HALO>::TOTAL, st, a1, a2, w, om, rm, p);
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
 }
