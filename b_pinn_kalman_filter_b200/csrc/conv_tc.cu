@@ -55,16 +55,20 @@ struct ConvTcParams {
   int stat_slots;
 };
 
-template <int BN, bool HALO = false>
+// DS (1x1 convolutions: a handful of K blocks per tile, so the kernel is bound by its epilogue, not by the operand
+// pipeline): one operand stage fewer and TWO output staging buffers, so that a pass never waits for the previous
+// pass's TMA store to drain the buffer and the residual tile of the next pass is in flight during this one.
+template <int BN, bool HALO = false, bool DS = false>
 struct TcSmem {
   static constexpr int A_BYTES = TC_BM * TC_BK * 2;            // 16 KB
   static constexpr int B_BYTES = BN * TC_BK * 2;               // 32 KB (BN = 256)
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int STAGES = ((BN == 256) ? 4 : (BN == 128 ? 6 : 8)) - (DS ? 1 : 0);
   static constexpr int TMEM_COLS = (2 * BN < 32) ? 32 : 2 * BN;
   // output staging for the TMA-store epilogue: BN/64 boxes of [128 pixels x 64 channels] bf16 (SW128), EPI 0 only
   static constexpr int OUT_OFF = STAGES * STAGE_BYTES;
-  static constexpr int OUT_BYTES = (BN >= 128) ? TC_BM * 128 * 2 : 0;   // 128 columns per pass (2 passes for BN = 256)
+  static constexpr int OUT_BUF = TC_BM * 128 * 2;              // 128 columns per pass (2 passes for BN = 256)
+  static constexpr int OUT_BYTES = (BN >= 128) ? OUT_BUF * (DS ? 2 : 1) : 0;
   static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;           // barriers + tmem slot, + slack for 1024 B alignment
 };
@@ -77,8 +81,8 @@ struct TcSmem {
 // Activation ingress drops from 9 x 16 KB to 3 x 18 KB per K block (x 3.4 instead of x 9).  Weights ride a separate
 // ring (one 16 KB box per tap) filled by their own producer warp.
 constexpr int HALO_TW = 8, HALO_TH = 16;
-template <int BN>
-struct TcSmem<BN, true> {
+template <int BN, bool DS>
+struct TcSmem<BN, true, DS> {
   static constexpr int BOX_BYTES = (HALO_TH + 2) * HALO_TW * 128;      // 18 KB
   static constexpr int A_BYTES = 3 * BOX_BYTES;                        // 54 KB per K block
   static constexpr int B_BYTES = BN * TC_BK * 2;
@@ -87,18 +91,40 @@ struct TcSmem<BN, true> {
   static constexpr int W_OFF = STAGES * A_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int OUT_OFF = W_OFF + WSTAGES * B_BYTES;
-  static constexpr int OUT_BYTES = TC_BM * 128 * 2;
+  static constexpr int OUT_BUF = TC_BM * 128 * 2;
+  static constexpr int OUT_BYTES = OUT_BUF;
   static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;
   static constexpr int STAGE_BYTES = 0;
 };
 
-template <int BN, int EPI, bool HALO = false>
+// Pair variant (cta_group::2, Cout tile 256): a 128 x 256 tile streams 48 KB per K block per SM, two thirds of it
+// weights that every CTA fetches again for every tile, and L2 cannot feed that to 148 SMs (the MMA issuer waited 33-36 %
+// of its time for operand stages, profiles/r01f_conv_tc_roles.txt).  Two SMs of a TPC now run one 256 x 256 tile: each
+// loads its own 128 pixels and HALF of the weight tile (32 KB per K block per SM), and six stages fit.
+struct TcSmemPair {
+  static constexpr int A_BYTES = TC_BM * TC_BK * 2;            // 16 KB
+  static constexpr int B_BYTES = 128 * TC_BK * 2;              // 16 KB: this CTA's half of the 256 weight rows
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = 6;
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int OUT_OFF = STAGES * STAGE_BYTES;
+  static constexpr int OUT_BUF = TC_BM * 128 * 2;
+  static constexpr int OUT_BYTES = OUT_BUF;
+  static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+};
+template <int BN, bool HALO, bool DS, bool PAIR> struct TcSmemSel { using type = TcSmem<BN, HALO, DS>; };
+template <int BN, bool HALO, bool DS> struct TcSmemSel<BN, HALO, DS, true> { using type = TcSmemPair; };
+
+template <int BN, int EPI, bool HALO = false, bool DS = false, bool PAIR = false>
 __global__ void __launch_bounds__(TC_THREADS + (HALO ? 32 : 0), 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapOut,
                const __grid_constant__ CUtensorMap mapRes, const ConvTcParams p) {
-  using S = TcSmem<BN, HALO>;
+  using S = typename TcSmemSel<BN, HALO, DS, PAIR>::type;
+  static_assert(!PAIR || (BN == 256 && EPI == 0 && !HALO && !DS), "pair variant: 256-wide tiles, plain epilogue");
+  const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
   constexpr int NWS = HALO ? TcSmem<BN, true>::WSTAGES : 0;     // weight-ring stages (halo variant only)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -120,10 +146,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   const int taps = p.taps_w * p.taps_w;
   const int num_kb = taps * kb_per_tap;
   const int num_tiles = p.num_m * p.num_n;
+  // work items: tiles, round robin over CTAs; PAIR: pairs of M tiles (2 pm, 2 pm + 1), round robin over CTA pairs
+  const int tile_first = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int tile_step = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int tile_end = PAIR ? ((p.num_m + 1) / 2) * p.num_n : num_tiles;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 8); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), PAIR ? 16 : 8); }   // PAIR: both CTAs' epilogue warps
     for (int w = 0; w < NWS; ++w) { mbar_init(wfull_bar(w), 1); mbar_init(wempty_bar(w), 1); }
     mbar_init(res_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -131,17 +161,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
   }
   if (warp == 1) {
+    if constexpr (PAIR) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(S::TMEM_COLS));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    } else {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "n"(S::TMEM_COLS));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();   // PAIR: the peer's barriers are initialised too
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
   b200_pdl_wait();   // everything above overlapped the previous kernel's tail; its outputs are read from here on
   b200_pdl_trigger();
 
-  auto tile_coords = [&](int tile, int& mt, int& nt) { nt = tile % p.num_n; mt = tile / p.num_n; };
+  auto tile_coords = [&](int tile, int& mt, int& nt) {
+    nt = tile % p.num_n; mt = tile / p.num_n;
+    if constexpr (PAIR) mt = 2 * mt + (int)cta_rank;      // an odd tail tile lies beyond the batch: TMA zero-fills / clips
+  };
   auto m_origin = [&](int mt, int& b0, int& h0, int& w0) {
     if (p.TB > 1) { b0 = mt * p.TB; h0 = 0; w0 = 0; return; }
     const int per_img = p.tiles_w * p.tiles_h;
@@ -155,7 +193,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     // ================= TMA producer =================
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile_first; tile < tile_end; tile += tile_step) {
         int mt, nt, b0, h0, w0;
         tile_coords(tile, mt, nt);
         m_origin(mt, b0, h0, w0);
@@ -179,11 +217,20 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           for (int kb = 0; kb < kb_per_tap; ++kb) {
             mbar_wait(empty_bar(stage), phase ^ 1);
             const uint32_t sa = base + stage * S::STAGE_BYTES, sb = sa + S::A_BYTES;
-            mbar_expect_tx(full_bar(stage), S::STAGE_BYTES);
             const int c = kb * TC_BK;
+            if constexpr (PAIR) {
+              // both CTAs' boxes complete on the LEADER's barrier, which expects the bytes of the whole pair
+              const uint32_t lbar = mapa_cta(full_bar(stage), 0);
+              if (cta_rank == 0) mbar_expect_tx(full_bar(stage), 2 * S::STAGE_BYTES);
+              if (c < p.C1) tma_load_4d_2sm(sa, &mapA1, lbar, c, w0 * p.stride + s - p.pad, h0 * p.stride + r - p.pad, b0);
+              else tma_load_4d_2sm(sa, &mapA2, lbar, c - p.C1, w0 * p.stride + s - p.pad, h0 * p.stride + r - p.pad, b0);
+              tma_load_2d_2sm(sb, &mapW, lbar, tap * Ctot + c, nt * BN + (int)cta_rank * 128);
+            } else {
+            mbar_expect_tx(full_bar(stage), S::STAGE_BYTES);
             if (c < p.C1) tma_load_4d(sa, &mapA1, full_bar(stage), c, w0 * p.stride + s - p.pad, h0 * p.stride + r - p.pad, b0);
             else tma_load_4d(sa, &mapA2, full_bar(stage), c - p.C1, w0 * p.stride + s - p.pad, h0 * p.stride + r - p.pad, b0);
             tma_load_2d(sb, &mapW, full_bar(stage), tap * Ctot + c, nt * BN);
+            }
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -195,7 +242,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     if constexpr (HALO) {
       if (lane == 0) {
         int ws = 0; uint32_t wphase = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        for (int tile = tile_first; tile < tile_end; tile += tile_step) {
           int mt, nt;
           tile_coords(tile, mt, nt);
           for (int kb = 0; kb < kb_per_tap; ++kb)
@@ -210,14 +257,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0) {
-      // instruction descriptor: D = f32, A = B = bf16, both K-major, N = BN, M = 128
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+    if (lane == 0 && cta_rank == 0) {
+      // instruction descriptor: D = f32, A = B = bf16, both K-major, N = BN, M = 128 (PAIR: 256 over the two CTAs)
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
+                             ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24);
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       int ws = 0; uint32_t wphase = 0;          // weight ring (halo variant)
       (void)ws; (void)wphase;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile_first; tile < tile_end; tile += tile_step) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
@@ -250,13 +298,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 #pragma unroll
           for (int k = 0; k < TC_BK / 16; ++k) {
             // advance 16 elements (32 B) along K inside the 128 B swizzle row: +2 in the 16-byte-unit address field
-            tc_mma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+            if constexpr (PAIR) tc_mma_bf16_2sm(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+            else tc_mma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
           }
-          tc_commit(empty_bar(stage));
+          if constexpr (PAIR) tc_commit_2sm(empty_bar(stage)); else tc_commit(empty_bar(stage));
           if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
         }
-        tc_commit(tfull_bar(acc));
+        if constexpr (PAIR) tc_commit_2sm(tfull_bar(acc)); else tc_commit(tfull_bar(acc));
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -271,18 +320,20 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     // (profiles/r01f_conv_tc_roles.txt).  Instead the residual tile is fetched by TMA INTO the output staging buffer
     // (same box, same SW128 layout) one pass ahead; each thread then reads the 16-byte units it is about to overwrite.
     uint32_t res_phase = 0;
-    auto res_fetch = [&](int tile_, int pass_) {           // thread 64 only
+    auto res_fetch = [&](int tile_, int pass_, int buf_) {           // thread 64 only
       int mt_, nt_, b0_, h0_, w0_;
       tile_coords(tile_, mt_, nt_);
       m_origin(mt_, b0_, h0_, w0_);
+      const uint32_t dst = base + S::OUT_OFF + buf_ * S::OUT_BUF;
       mbar_expect_tx(res_bar, 2 * TC_BM * 128);
-      tma_load_4d(base + S::OUT_OFF, &mapRes, res_bar, nt_ * BN + pass_ * 128, w0_, h0_, b0_);
-      tma_load_4d(base + S::OUT_OFF + TC_BM * 128, &mapRes, res_bar, nt_ * BN + pass_ * 128 + 64, w0_, h0_, b0_);
+      tma_load_4d(dst, &mapRes, res_bar, nt_ * BN + pass_ * 128, w0_, h0_, b0_);
+      tma_load_4d(dst + TC_BM * 128, &mapRes, res_bar, nt_ * BN + pass_ * 128 + 64, w0_, h0_, b0_);
     };
     if constexpr (EPI == 0) {
-      if (p.res && threadIdx.x == 64 && (int)blockIdx.x < num_tiles) res_fetch(blockIdx.x, 0);
+      if (p.res && threadIdx.x == 64 && tile_first < tile_end) res_fetch(tile_first, 0, 0);
     }
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    int pcount = 0;                                      // passes done by this CTA (DS: staging buffer = pcount & 1)
+    for (int tile = tile_first; tile < tile_end; tile += tile_step) {
       int mt, nt, b0, h0, w0;
       tile_coords(tile, mt, nt);
       m_origin(mt, b0, h0, w0);
@@ -330,19 +381,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 #pragma unroll 1
       for (int pass = 0; pass < BN / 128; ++pass) {
       const int cbeg = pass * 128 + half * CH;
+      const int sofs = S::OUT_OFF + (DS ? (pcount & 1) * S::OUT_BUF : 0);   // this pass's staging buffer
       if (p.res) {
         mbar_wait(res_bar, res_phase);                 // staging buffer holds this pass's residual tile
         res_phase ^= 1;
-      } else {
-        if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-        asm volatile("bar.sync 1, 256;" ::: "memory");  // staging buffer free (the previous store has read it)
       }
 #pragma unroll 1
       for (int c0 = cbeg; c0 < cbeg + CH; c0 += 32) {
         uint32_t r[32];
         tc_ld32(t_addr + c0, r);
         // this thread's row of the [128 x 64] SW128 box of the 64-channel group: unit u of row r sits at u ^ (r & 7)
-        uint8_t* srow = smem_raw + (base - smem_u32(smem_raw)) + S::OUT_OFF + ((c0 >> 6) & 1) * (TC_BM * 128) + m_local * 128;
+        uint8_t* srow = smem_raw + (base - smem_u32(smem_raw)) + sofs + ((c0 >> 6) & 1) * (TC_BM * 128) + m_local * 128;
         uint4 rv[4];
         if (p.res) {
 #pragma unroll
@@ -350,6 +399,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             rv[j] = *reinterpret_cast<const uint4*>(srow + (((((c0 & 63) >> 3) + j) ^ (m_local & 7)) << 4));
         }
         tc_wait_ld();
+        if (!p.res && c0 == cbeg) {                      // (uniform) staging buffer free: the previous store has read it
+          if (threadIdx.x == 64) {
+            if constexpr (DS) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // the store before last
+            else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          }
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
         if (valid) {
           float v[32];
 #pragma unroll
@@ -395,30 +451,61 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       if (pass == BN / 128 - 1) {                      // last TMEM read of this tile done: hand the accumulator back
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar(acc));
+        if (lane == 0) {
+          if constexpr (PAIR) mbar_arrive_cluster(mapa_cta(tempty_bar(acc), 0));   // the leader's barrier counts both CTAs
+          else mbar_arrive(tempty_bar(acc));
+        }
       }
       fence_proxy_async_smem();                        // generic-proxy smem writes -> visible to the TMA store
       asm volatile("bar.sync 1, 256;" ::: "memory");
       if (threadIdx.x == 64) {
-        tma_store_4d(base + S::OUT_OFF, &mapOut, nt * BN + pass * 128, w0, h0, b0);
-        tma_store_4d(base + S::OUT_OFF + TC_BM * 128, &mapOut, nt * BN + pass * 128 + 64, w0, h0, b0);
+        tma_store_4d(base + sofs, &mapOut, nt * BN + pass * 128, w0, h0, b0);
+        tma_store_4d(base + sofs + TC_BM * 128, &mapOut, nt * BN + pass * 128 + 64, w0, h0, b0);
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        if constexpr (DS) {
+          // the OTHER buffer is idle once the previous pass's store has read it (every thread is past that pass's
+          // column sums: it went through the barrier above): fetch the next pass's residual tile into it now
+          const bool last_pass = pass == BN / 128 - 1;
+          if (p.res && (!last_pass || tile + tile_step < tile_end)) {
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            if (last_pass) res_fetch(tile + tile_step, 0, (pcount + 1) & 1); else res_fetch(tile, pass + 1, (pcount + 1) & 1);
+          }
+        }
       }
       if (p.stats) {
         // column sums over the staged tile: thread = (column, 64-row half); fixed order -> bit-reproducible
         const int et = threadIdx.x - 64, col = et & 127, rh = et >> 7;
-        const uint8_t* sbox = smem_raw + (base - smem_u32(smem_raw)) + S::OUT_OFF + (col >> 6) * (TC_BM * 128);
+        const uint8_t* sbox = smem_raw + (base - smem_u32(smem_raw)) + sofs + (col >> 6) * (TC_BM * 128);
         const int unit = (col & 63) >> 3, sub = (col & 7) * 2;
         const int rows_img = p.TW * p.TH;                  // rows of one image inside the tile (128 when TB == 1)
         const int seg = rows_img < 64 ? rows_img : 64;
         const int ch = nt * BN + pass * 128 + col;
+        // row r of the box keeps this column at r * 128 + ((unit ^ (r & 7)) << 4) + sub; segments start at multiples of
+        // 8 rows, so the eight swizzled offsets of an 8-row group are fixed per thread.  Even / odd rows accumulate
+        // separately (two dependency chains instead of one); the order is fixed, so results stay reproducible.
+        int off8[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) off8[i] = i * 128 + ((unit ^ i) << 4) + sub;
         for (int r0 = rh * 64; r0 < rh * 64 + 64; r0 += seg) {
-          float s1 = 0.f, s2 = 0.f;
-          for (int r = r0; r < r0 + seg; ++r) {
-            const bf16 hv = *reinterpret_cast<const bf16*>(sbox + r * 128 + ((unit ^ (r & 7)) << 4) + sub);
-            const float f = __bfloat162float(hv);
-            s1 += f; s2 = fmaf(f, f, s2);
+          float s1 = 0.f, s2 = 0.f, t1 = 0.f, t2 = 0.f;
+          if (seg < 8) {                                   // images smaller than 8 pixels: plain loop
+            for (int r = r0; r < r0 + seg; ++r) {
+              const float f = __bfloat162float(*reinterpret_cast<const bf16*>(sbox + r * 128 + ((unit ^ (r & 7)) << 4) + sub));
+              s1 += f; s2 = fmaf(f, f, s2);
+            }
+          } else
+          for (int r = r0; r < r0 + seg; r += 8) {
+            const uint8_t* rb = sbox + r * 128;
+            float f[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = __bfloat162float(*reinterpret_cast<const bf16*>(rb + off8[i]));
+#pragma unroll
+            for (int i = 0; i < 8; i += 2) {
+              s1 += f[i]; s2 = fmaf(f[i], f[i], s2);
+              t1 += f[i + 1]; t2 = fmaf(f[i + 1], f[i + 1], t2);
+            }
           }
+          s1 += t1; s2 += t2;
           int bi, slot;
           if (p.TB > 1) { bi = b0 + r0 / rows_img; slot = 0; }
           else { bi = b0; slot = ((h0 / p.TH) * p.tiles_w + w0 / p.TW) * 2 + rh; }
@@ -428,16 +515,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           }
         }
       }
-      if (p.res) {
+      if (!DS && p.res) {
         // next pass's residual tile: once the store above has read the staging buffer and the column sums are done
         const bool last_pass = pass == BN / 128 - 1;
-        const bool more = !last_pass || tile + (int)gridDim.x < num_tiles;
+        const bool more = !last_pass || tile + tile_step < tile_end;
         if (p.stats) asm volatile("bar.sync 1, 256;" ::: "memory");
         if (threadIdx.x == 64 && more) {
           asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-          if (last_pass) res_fetch(tile + gridDim.x, 0); else res_fetch(tile, pass + 1);
+          if (last_pass) res_fetch(tile + tile_step, 0, 0); else res_fetch(tile, pass + 1, 0);
         }
       }
+      ++pcount;
       }
       }
       if constexpr (EPI == 1) {
@@ -450,9 +538,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   }
   if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tc_fence_before();
-  __syncthreads();
+  if constexpr (PAIR) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
+    if constexpr (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(S::TMEM_COLS));
+    else
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(S::TMEM_COLS));
   }
 }
@@ -535,7 +625,7 @@ bool tile_box(int B, int H, int W, int& TW, int& TH, int& TB, int& tiles_w, int&
   return TB <= 256;
 }
 
-template <int BN, int EPI, bool HALO = false>
+template <int BN, int EPI, bool HALO = false, bool DS = false>
 int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
            const ConvTcParams& p, cudaStream_t st) {
   // residual tiles are fetched with the geometry of the output boxes (same tensor shape, other base pointer)
@@ -547,21 +637,61 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_tc_kernel<BN, EPI, HALO>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    TcSmem<BN, HALO>::TOTAL);
+    attr_err = cudaFuncSetAttribute(conv_tc_kernel<BN, EPI, HALO, DS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    TcSmem<BN, HALO, DS>::TOTAL);
   });
   if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
-  cudaError_t le = b200_launch_pdl(conv_tc_kernel<BN, EPI, HALO>, dim3(grid), dim3(TC_THREADS + (HALO ? 32 : 0)),
-                                   (size_t)TcSmem<BN, HALO>::TOTAL, st, a1, a2, w, om, rm, p);
+  cudaError_t le = b200_launch_pdl(conv_tc_kernel<BN, EPI, HALO, DS>, dim3(grid), dim3(TC_THREADS + (HALO ? 32 : 0)),
+                                   (size_t)TcSmem<BN, HALO, DS>::TOTAL, st, a1, a2, w, om, rm, p);
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
+}
+
+int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
+                const ConvTcParams& p, cudaStream_t st) {
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  auto kern = conv_tc_kernel<256, 0, false, false, true>;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmemPair::TOTAL);
+  });
+  if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
+  CUtensorMap rm = om;
+  if (p.res) {
+    const int rc = act_map(&rm, p.res, p.B, p.H, p.W, p.Cout, p.TW, p.TH, p.TB);
+    if (rc) return rc;
+  }
+  const int pairs = ((p.num_m + 1) / 2) * p.num_n;
+  const int clusters = pairs < B200_NUM_SMS / 2 ? pairs : B200_NUM_SMS / 2;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(TC_THREADS); cfg.dynamicSmemBytes = TcSmemPair::TOTAL;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, a1, a2, w, om, rm, p);
+  if (le != cudaSuccess) return -(1000 + (int)le);
+  B200_RETURN_LAST();
+}
+
+// CTA-pair variant for 3x3 convolutions with 256-wide tiles (B200_CONV_PAIR=0 disables it: A/B measurements)
+bool pair_enabled() {
+  static const bool on = [] { const char* e = getenv("B200_CONV_PAIR"); return !(e && e[0] == '0'); }();
+  return on;
 }
 
 // halo variant on / off (B200_CONV_HALO=0 disables it: A/B measurements)
 bool halo_enabled() {
   static const bool on = [] { const char* e = getenv("B200_CONV_HALO"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
+// double-buffered output staging for 1x1 convolutions on / off (B200_CONV_DS=0 disables it: A/B measurements)
+bool ds_enabled() {
+  static const bool on = [] { const char* e = getenv("B200_CONV_DS"); return !(e && e[0] == '0'); }();
   return on;
 }
 
@@ -658,6 +788,14 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   }
   rc = act_map(&om, out, B, H, W, Cout, p.TW, p.TH, p.TB);
   if (rc) return rc;
+  if (ksize == 3 && BN == 256 && pair_enabled()) {
+    CUtensorMap wh;                                       // each CTA of the pair loads 128 of the 256 weight rows
+    rc = weight_map(&wh, w, Cout, Ktot, 128);
+    if (rc) return rc;
+    return launch_pair(a1, a2, wh, om, p, st);
+  }
+  if (ksize == 1 && ds_enabled())     // epilogue-bound: double-buffered staging
+    return BN == 256 ? launch<256, 0, false, true>(a1, a2, wm, om, p, st) : launch<128, 0, false, true>(a1, a2, wm, om, p, st);
   return BN == 256 ? launch<256, 0>(a1, a2, wm, om, p, st) : launch<128, 0>(a1, a2, wm, om, p, st);
 }
 

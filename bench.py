@@ -346,8 +346,18 @@ def run_b200(a):
     dom = max(conv_names, key=lambda n: table[n][1]) if conv_names else top
     n_l, d_ms, d_fl = table[dom]
     achieved = d_fl / (d_ms * 1e-3) / 1e12 if d_ms > 0 else 0.0
+    # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this command
+    # (profiles/summarize_ncu.py full ...); null when no capture is committed
+    traffic, traffic_src = None, None
+    tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "conv_tc_traffic.json")
+    if dom.startswith("b200_conv2d_tc") and os.path.exists(tpath):
+        with open(tpath) as f:
+            tj = json.load(f)
+        traffic, traffic_src = tj.get("dram_bytes_per_launch"), "profiles/conv_tc_traffic.json (%s, %d launches)" % (
+            tj.get("source", "ncu --set full"), tj.get("launches", 0))
     roof = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tc_sustained"], "unit": "TFLOP/s",
-            "frac": achieved / pk["tc_sustained"], "traffic": None, "peak_source": pk["source"] + " (sustained bf16)",
+            "frac": achieved / pk["tc_sustained"], "traffic": traffic, "traffic_unit": "bytes per launch (DRAM read + write)",
+            "traffic_source": traffic_src, "peak_source": pk["source"] + " (sustained bf16)",
             "launches_per_forward": n_l, "avg_launch_ms": d_ms / max(n_l, 1),
             "flops_per_forward": d_fl, "share_of_forward": d_ms / fwd_ms if fwd_ms else None}
     breakdown = {n: {"launches": v[0], "ms": round(v[1], 4), "gflop": round(v[2] / 1e9, 3)} for n, v in

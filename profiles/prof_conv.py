@@ -18,10 +18,11 @@ out = torch.empty(B, H, H, Cout, device=dev, dtype=torch.bfloat16)
 lib = _lib.lib()
 T = lib.b200_conv2d_tc_stat_slots(B, H, H)
 stats = torch.empty(B, T, Cout, 2, device=dev)
+res = torch.randn(B, H, H, Cout, device=dev).to(torch.bfloat16) if os.environ.get("RES", "0") == "1" else None
 
 
 def run():
-    _lib.check(lib.b200_conv2d_tc(_lib.ptr(x1), C1, _lib.ptr(x2), C2, _lib.ptr(w), _lib.ptr(bias), None, 0, None, 1.0,
+    _lib.check(lib.b200_conv2d_tc(_lib.ptr(x1), C1, _lib.ptr(x2), C2, _lib.ptr(w), _lib.ptr(bias), None, 0, _lib.ptr(res), 1.0,
                                   _lib.ptr(out), 0, None, _lib.ptr(stats) if os.environ.get("STATS", "1") == "1" else None, B, H, H, Cout, k, _lib.stream()), "conv")
 
 

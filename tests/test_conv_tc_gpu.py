@@ -17,6 +17,9 @@ SHAPES = [  # B, H, W, C1, C2, Cout, k
     (160, 16, 16, 256, 128, 256, 3),  # more tiles than SMs: persistent loop + both TMEM buffers
     (83, 32, 32, 128, 128, 128, 3),   # Cout = 128 with many tiles: paired M tiles per CTA (MT = 2)
     (1190, 8, 8, 128, 0, 128, 1),     # MT = 2 with an odd number of 2-image M tiles (last group half empty)
+    (297, 8, 8, 256, 0, 256, 3),      # CTA-pair variant (cta_group::2), odd number of M tiles: the last pair is half empty
+    (1186, 4, 4, 256, 256, 256, 3),   # CTA-pair variant, 8-image tiles, ragged batch, two sources
+    (152, 16, 16, 256, 0, 512, 3),    # CTA-pair variant, two 256-wide N tiles
 ]
 
 
