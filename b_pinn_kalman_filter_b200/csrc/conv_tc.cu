@@ -87,6 +87,7 @@ struct TcSmem<BN, true, DS> {
   static constexpr int A_BYTES = 3 * BOX_BYTES;                        // 54 KB per K block
   static constexpr int B_BYTES = BN * TC_BK * 2;
   static constexpr int STAGES = 2;                                     // activation stages
+  static constexpr int WGROUP = 1;                                     // taps per weight-ring stage
   static constexpr int WSTAGES = 5;                                    // weight ring (5 x 16 KB: what fits beside 2 x 54 KB)
   static constexpr int W_OFF = STAGES * A_BYTES;
   static constexpr int TMEM_COLS = 2 * BN;
@@ -114,8 +115,31 @@ struct TcSmemPair {
   static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;
 };
+// Pair + halo (Cout tile 128): a single SM's 128 x 128 x 16 MMA reads 4 KB of A and 4 KB of B per 64 clk, i.e. all of
+// the 128 B/clk shared memory delivers; as half of a 256 x 128 pair MMA it reads 4 + 2 KB.  Each CTA loads 64 of the
+// 128 weight rows per tap (8 KB boxes); a ring stage holds one filter ROW (3 taps, 24 KB), so the single MMA-issuing
+// thread -- whose per-tap barrier traffic is what paces N = 128 tiles -- waits and commits 6 instead of 18 times per tile.
+template <bool DS>
+struct TcSmemHaloPairT {
+  static constexpr int BOX_BYTES = (HALO_TH + 2) * HALO_TW * 128;
+  static constexpr int A_BYTES = 3 * BOX_BYTES;
+  static constexpr int B_BYTES = 64 * TC_BK * 2;               // 8 KB
+  static constexpr int STAGES = 2;
+  static constexpr int WGROUP = 3;                             // taps per weight-ring stage: one filter row
+  static constexpr int WSTAGES = DS ? 2 : 3;                   // DS: a ring stage makes room for the second staging buffer
+  static constexpr int W_OFF = STAGES * A_BYTES;
+  static constexpr int TMEM_COLS = 256;
+  static constexpr int OUT_OFF = W_OFF + WSTAGES * WGROUP * B_BYTES;
+  static constexpr int OUT_BUF = TC_BM * 128 * 2;
+  static constexpr int OUT_BYTES = OUT_BUF * (DS ? 2 : 1);
+  static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+  static constexpr int STAGE_BYTES = 0;
+};
 template <int BN, bool HALO, bool DS, bool PAIR> struct TcSmemSel { using type = TcSmem<BN, HALO, DS>; };
-template <int BN, bool HALO, bool DS> struct TcSmemSel<BN, HALO, DS, true> { using type = TcSmemPair; };
+template <int BN, bool DS> struct TcSmemSel<BN, false, DS, true> { using type = TcSmemPair; };
+template <int BN, bool DS> struct TcSmemSel<BN, true, DS, true> { using type = TcSmemHaloPairT<DS>; };
+using TcSmemHaloPair = TcSmemHaloPairT<false>;
 
 template <int BN, int EPI, bool HALO = false, bool DS = false, bool PAIR = false>
 __global__ void __launch_bounds__(TC_THREADS + (HALO ? 32 : 0), 1)
@@ -123,9 +147,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
                const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapOut,
                const __grid_constant__ CUtensorMap mapRes, const ConvTcParams p) {
   using S = typename TcSmemSel<BN, HALO, DS, PAIR>::type;
-  static_assert(!PAIR || (BN == 256 && EPI == 0 && !HALO && !DS), "pair variant: 256-wide tiles, plain epilogue");
+  static_assert(!PAIR || (EPI == 0 && ((BN == 256 && !HALO && !DS) || (BN == 128 && HALO))), "pair variants");
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
-  constexpr int NWS = HALO ? TcSmem<BN, true>::WSTAGES : 0;     // weight-ring stages (halo variant only)
+  constexpr int NWS = HALO ? (PAIR ? TcSmemHaloPairT<DS>::WSTAGES : TcSmem<BN, true>::WSTAGES) : 0;   // weight ring (halo)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar0 = base + S::BAR_OFF;
@@ -202,12 +226,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           for (int kb = 0; kb < kb_per_tap; ++kb) {
             mbar_wait(empty_bar(stage), phase ^ 1);
             const uint32_t sa = base + stage * S::A_BYTES;
-            mbar_expect_tx(full_bar(stage), S::A_BYTES);
             const int c = kb * TC_BK;
+            if constexpr (PAIR) {
+              const uint32_t lbar = mapa_cta(full_bar(stage), 0);
+              if (cta_rank == 0) mbar_expect_tx(full_bar(stage), 2 * S::A_BYTES);
+#pragma unroll
+              for (int sx = 0; sx < 3; ++sx) {
+                if (c < p.C1) tma_load_4d_2sm(sa + sx * S::BOX_BYTES, &mapA1, lbar, c, w0 + sx - 1, h0 - 1, b0);
+                else tma_load_4d_2sm(sa + sx * S::BOX_BYTES, &mapA2, lbar, c - p.C1, w0 + sx - 1, h0 - 1, b0);
+              }
+            } else {
+            mbar_expect_tx(full_bar(stage), S::A_BYTES);
 #pragma unroll
             for (int sx = 0; sx < 3; ++sx) {
               if (c < p.C1) tma_load_4d(sa + sx * S::BOX_BYTES, &mapA1, full_bar(stage), c, w0 + sx - 1, h0 - 1, b0);
               else tma_load_4d(sa + sx * S::BOX_BYTES, &mapA2, full_bar(stage), c - p.C1, w0 + sx - 1, h0 - 1, b0);
+            }
             }
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
@@ -246,10 +280,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           int mt, nt;
           tile_coords(tile, mt, nt);
           for (int kb = 0; kb < kb_per_tap; ++kb)
-            for (int tap = 0; tap < 9; ++tap) {
+            for (int tap = 0; tap < 9; tap += S::WGROUP) {
               mbar_wait(wempty_bar(ws), wphase ^ 1);
-              mbar_expect_tx(wfull_bar(ws), S::B_BYTES);
-              tma_load_2d(base + S::W_OFF + ws * S::B_BYTES, &mapW, wfull_bar(ws), tap * Ctot + kb * TC_BK, nt * BN);
+              const uint32_t wdst = base + S::W_OFF + ws * (S::WGROUP * S::B_BYTES);
+              if constexpr (PAIR) {
+                const uint32_t lbar = mapa_cta(wfull_bar(ws), 0);
+                if (cta_rank == 0) mbar_expect_tx(wfull_bar(ws), 2 * S::WGROUP * S::B_BYTES);
+#pragma unroll
+                for (int g = 0; g < S::WGROUP; ++g)
+                  tma_load_2d_2sm(wdst + g * S::B_BYTES, &mapW, lbar, (tap + g) * Ctot + kb * TC_BK,
+                                  nt * BN + (int)cta_rank * (BN / 2));
+              } else {
+              mbar_expect_tx(wfull_bar(ws), S::WGROUP * S::B_BYTES);
+#pragma unroll
+              for (int g = 0; g < S::WGROUP; ++g)
+                tma_load_2d(wdst + g * S::B_BYTES, &mapW, wfull_bar(ws), (tap + g) * Ctot + kb * TC_BK, nt * BN);
+              }
               if (++ws == NWS) { ws = 0; wphase ^= 1; }
             }
         }
@@ -274,19 +320,28 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             mbar_wait(full_bar(stage), phase);
             tc_fence_after();
             const uint32_t sa = base + stage * S::A_BYTES;
-            for (int tap = 0; tap < 9; ++tap) {
-              const int r = tap / 3, sx = tap - r * 3;
+            const uint64_t da0 = make_sw128_desc(sa);
+#pragma unroll
+            for (int tap0 = 0; tap0 < 9; tap0 += S::WGROUP) {
               mbar_wait(wfull_bar(ws), wphase);
               tc_fence_after();
-              const uint64_t da = make_sw128_desc(sa + sx * S::BOX_BYTES + r * (HALO_TW * 128));
-              const uint64_t db = make_sw128_desc(base + S::W_OFF + ws * S::B_BYTES);
+              const uint64_t db0 = make_sw128_desc(base + S::W_OFF + ws * (S::WGROUP * S::B_BYTES));
 #pragma unroll
-              for (int k = 0; k < TC_BK / 16; ++k)
-                tc_mma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | tap | k) != 0 ? 1u : 0u);
-              tc_commit(wempty_bar(ws));
+              for (int g = 0; g < S::WGROUP; ++g) {
+                const int tap = tap0 + g, r = tap / 3, sx = tap - r * 3;
+                // descriptor start addresses are in 16-byte units: constant offsets per tap once unrolled
+                const uint64_t da = da0 + (uint64_t)((sx * S::BOX_BYTES + r * (HALO_TW * 128)) >> 4);
+                const uint64_t db = db0 + (uint64_t)((g * S::B_BYTES) >> 4);
+#pragma unroll
+                for (int k = 0; k < TC_BK / 16; ++k) {
+                  if constexpr (PAIR) tc_mma_bf16_2sm(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | tap | k) != 0 ? 1u : 0u);
+                  else tc_mma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | tap | k) != 0 ? 1u : 0u);
+                }
+              }
+              if constexpr (PAIR) tc_commit_2sm(wempty_bar(ws)); else tc_commit(wempty_bar(ws));
               if (++ws == NWS) { ws = 0; wphase ^= 1; }
             }
-            tc_commit(empty_bar(stage));
+            if constexpr (PAIR) tc_commit_2sm(empty_bar(stage)); else tc_commit(empty_bar(stage));
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
         } else {
@@ -649,13 +704,15 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
   B200_RETURN_LAST();
 }
 
+template <int BN, bool HALO, bool DS = false>
 int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
                 const ConvTcParams& p, cudaStream_t st) {
+  using SP = typename TcSmemSel<BN, HALO, DS, true>::type;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
-  auto kern = conv_tc_kernel<256, 0, false, false, true>;
+  auto kern = conv_tc_kernel<BN, 0, HALO, DS, true>;
   std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TcSmemPair::TOTAL);
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SP::TOTAL);
   });
   if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
   CUtensorMap rm = om;
@@ -666,7 +723,7 @@ int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap&
   const int pairs = ((p.num_m + 1) / 2) * p.num_n;
   const int clusters = pairs < B200_NUM_SMS / 2 ? pairs : B200_NUM_SMS / 2;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(TC_THREADS); cfg.dynamicSmemBytes = TcSmemPair::TOTAL;
+  cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(TC_THREADS + (HALO ? 32 : 0)); cfg.dynamicSmemBytes = SP::TOTAL;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -680,6 +737,11 @@ int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap&
 // CTA-pair variant for 3x3 convolutions with 256-wide tiles (B200_CONV_PAIR=0 disables it: A/B measurements)
 bool pair_enabled() {
   static const bool on = [] { const char* e = getenv("B200_CONV_PAIR"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
+bool halo_pair_enabled() {
+  static const bool on = [] { const char* e = getenv("B200_CONV_HALO_PAIR"); return !(e && e[0] == '0'); }();
   return on;
 }
 
@@ -784,6 +846,16 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
     else a2 = a1;
     rc = act_map(&om, out, B, H, W, Cout, HALO_TW, HALO_TH, 1);
     if (rc) return rc;
+    if (halo_pair_enabled()) {
+      CUtensorMap wh;                                     // each CTA of the pair loads 64 of the 128 weight rows
+      rc = weight_map(&wh, w, Cout, Ktot, 64);
+      if (rc) return rc;
+      // B200_CONV_HALO_PAIR_DS=1: second staging buffer instead of the third weight-ring stage for convs with a
+      // residual (measured: 128->128 0.304 -> 0.299 ms, 256->128 0.505 -> 0.529 ms; off)
+      static const bool hp_ds = [] { const char* e = getenv("B200_CONV_HALO_PAIR_DS"); return e && e[0] == '1'; }();
+      if (res && hp_ds) return launch_pair<128, true, true>(a1, a2, wh, om, p, st);
+      return launch_pair<128, true>(a1, a2, wh, om, p, st);
+    }
     return launch<128, 0, true>(a1, a2, wm, om, p, st);
   }
   rc = act_map(&om, out, B, H, W, Cout, p.TW, p.TH, p.TB);
@@ -792,7 +864,7 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
     CUtensorMap wh;                                       // each CTA of the pair loads 128 of the 256 weight rows
     rc = weight_map(&wh, w, Cout, Ktot, 128);
     if (rc) return rc;
-    return launch_pair(a1, a2, wh, om, p, st);
+    return launch_pair<256, false>(a1, a2, wh, om, p, st);
   }
   if (ksize == 1 && ds_enabled())     // epilogue-bound: double-buffered staging
     return BN == 256 ? launch<256, 0, false, true>(a1, a2, wm, om, p, st) : launch<128, 0, false, true>(a1, a2, wm, om, p, st);
