@@ -367,8 +367,10 @@ __global__ void __launch_bounds__(256) upfirdn2d_up2_kernel(const float* __restr
           o[2 * x + c] = acc;
         }
       float* op = out + (pl * out_h + 2 * j + a) * (long long)out_w + 2 * i0;
-      __stcs(reinterpret_cast<float4*>(op), make_float4(o[0], o[1], o[2], o[3]));        // written once, never re-read
-      __stcs(reinterpret_cast<float4*>(op + 4), make_float4(o[4], o[5], o[6], o[7]));
+      // one 256-bit streaming store per thread and row (sm_100): a whole 32-byte sector per request instead of two
+      // half-sector requests 16 bytes apart; written once, never re-read
+      asm volatile("st.global.cs.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(op), "f"(o[0]), "f"(o[1]), "f"(o[2]),
+                   "f"(o[3]), "f"(o[4]), "f"(o[5]), "f"(o[6]), "f"(o[7]) : "memory");
     }
   }
 }
