@@ -239,3 +239,75 @@ def to_flattened_numpy(x):
 
 def from_flattened_numpy(x, shape):
     return torch.from_numpy(x.reshape(shape))
+
+
+# ---- on-disk format: the reference's checkpoints (utils.py:84-128 `save_checkpoint` / `load_checkpoint`) ---------------
+# A checkpoint is `torch.save` of {'model': DataParallel state_dict (`module.all_modules.<i>.<name>`, `module.sigmas`),
+# 'ema': {'decay', 'num_updates', 'shadow_params': [tensor, ...]}, 'optimizer'..., 'step'}.  `shadow_params` follows
+# `model.parameters()` restricted to requires_grad (models/ema.py:28-29), i.e. nn.Module REGISTRATION order, which is
+# not the order of the forward walk: inside a block the reference registers GroupNorm_0, Conv_0, Dense_0, GroupNorm_1,
+# Dropout_0, Conv_1, then Conv_2 / NIN_0 (layerspp.py:166-192, 212-240, layers.py:611-634); attention registers
+# GroupNorm_0, NIN_0..3 (layerspp.py:62-73).  The frozen Fourier projection `all_modules.0.W`
+# (layerspp.py:37, requires_grad=False) has no shadow entry.
+_SUBMODULE_RANK = {"GroupNorm_0": 0, "Conv_0": 1, "Conv2d_0": 1, "Dense_0": 2, "GroupNorm_1": 3, "Conv_1": 5, "Conv_2": 6,
+                   "NIN_0": 6, "NIN_1": 7, "NIN_2": 8, "NIN_3": 9}
+_LEAF_RANK = {"weight": 0, "W": 0, "bias": 1, "b": 1}
+
+
+def trainable_parameter_order(config):
+    """Keys of the network's trainable parameters in the order of the reference's `model.parameters()` (what
+    `ExponentialMovingAverage.shadow_params` is indexed by).  Needs no device."""
+    from .engine import parameter_spec
+    spec, _ = parameter_spec(config, get_model(config.model.name))
+    fourier = str(getattr(config.model, "embedding_type", "positional")).lower() == "fourier"
+    keys = []
+    for key, _, _ in spec:
+        parts = key.split(".")          # all_modules.<i>[.<sub>].<leaf>
+        if parts[0] != "all_modules":
+            raise ValueError("unexpected parameter key %s" % key)
+        if fourier and key == "all_modules.0.W":
+            continue
+        sub = parts[2] if len(parts) == 4 else None
+        keys.append((int(parts[1]), _SUBMODULE_RANK[sub] if sub is not None else 0, _LEAF_RANK[parts[-1]], key))
+    return [k[3] for k in sorted(keys)]
+
+
+def ema_state_dict(config, ema_state, base=None):
+    """{key: tensor} from an `ExponentialMovingAverage.state_dict()` of the reference (models/ema.py:91-93) -- the
+    equivalent of `ema.copy_to(score_model.parameters())` (run_lib.py:172-175).  `base`: state dict providing the
+    entries EMA does not track (`sigmas`, the frozen Fourier projection)."""
+    order = trainable_parameter_order(config)
+    shadow = ema_state["shadow_params"]
+    if len(shadow) != len(order):
+        raise RuntimeError("EMA holds %d tensors, the network has %d trainable parameters" % (len(shadow), len(order)))
+    sd = {}
+    if base is not None:
+        for k, v in base.items():
+            sd[k[len("module."):] if k.startswith("module.") else k] = v
+    for k, v in zip(order, shadow):
+        sd[k] = v
+    return sd
+
+
+def checkpoint_state_dict(ckpt, config, use_ema=False, map_location="cpu"):
+    """State dict of a reference checkpoint (a path or the already loaded dict); use_ema=True returns the EMA weights
+    the reference samples with (run_lib.py:172-175, 380-383)."""
+    import os
+    if isinstance(ckpt, (str, os.PathLike)):
+        ckpt = torch.load(ckpt, map_location=map_location, weights_only=False)
+    model_sd = ckpt["model"]
+    if not use_ema:
+        return {k[len("module."):] if k.startswith("module.") else k: v for k, v in model_sd.items()}
+    return ema_state_dict(config, ckpt["ema"], base=model_sd)
+
+
+def load_checkpoint(ckpt_dir, model, device=None, use_ema=False):
+    """utils.load_checkpoint(ckpt_dir, model, device) (utils.py:96-106): warns and returns the model unchanged when the
+    file does not exist, else loads checkpoint['model'] (or, with use_ema=True, the EMA weights) into it."""
+    import logging
+    import os
+    if not os.path.exists(ckpt_dir):
+        logging.warning(f"No checkpoint found at {ckpt_dir}. Returned the same state as input")
+        return model
+    model.load_state_dict(checkpoint_state_dict(ckpt_dir, model.config, use_ema=use_ema))
+    return model

@@ -313,6 +313,34 @@ def main():
             gen_vjp(ns, n)
     if a.only in (None, "ode"):
         gen_ode(ns)
+    if a.only in (None, "param_order"):
+        gen_param_order(ns)
+
+
+CKPT_CONFIGS = {  # our config name -> reference config module
+    "ve/cifar10_ncsnpp_continuous": "configs.ve.cifar10_ncsnpp_continuous",
+    "vp/nc_ddpmpp": "configs.vp.nc_ddpmpp",
+    "ve/celebahq_256_ncsnpp_continuous": "configs.ve.celebahq_256_ncsnpp_continuous",
+    "vp/cifar10_ncsnpp_continuous": "configs.vp.cifar10_ncsnpp_continuous",
+}
+
+
+def gen_param_order(ns):
+    """Names of the REFERENCE networks' trainable parameters in `model.parameters()` order -- what the shadow_params
+    list of a checkpoint's EMA state is indexed by (models/ema.py:28-29, utils.py:109-128)."""
+    import hashlib
+    import json
+    out = {}
+    for ours, refm in CKPT_CONFIGS.items():
+        rcfg = ref_import.get_config(refm)
+        rcfg.device = torch.device("cpu")
+        m = ns.mutils.get_model(rcfg.model.name)(rcfg)
+        names = [n for n, p in m.named_parameters() if p.requires_grad]
+        out[ours] = {"count": len(names), "sha1": hashlib.sha1("\n".join(names).encode()).hexdigest(),
+                     "first": names[:12], "last": names[-4:]}
+    with open(os.path.join(GOLDEN, "param_order.json"), "w") as f:
+        json.dump(out, f, indent=1)
+    print("param_order", {k: v["count"] for k, v in out.items()})
 
 
 if __name__ == "__main__":

@@ -148,3 +148,26 @@ def test_graph_replay_equals_eager(cuda):
     assert torch.isfinite(outs[0]).all()
     assert torch.equal(outs[0], outs[1])
     assert not torch.equal(outs[0], torch.full(c["shape"], 3.0, device=cuda))
+
+
+def test_load_checkpoint_model_and_ema_weights(cuda, tmp_path):
+    """A checkpoint file in the reference's layout (utils.py:109-128): `model` entry with DataParallel keys, EMA shadow
+    list in registration order.  The EMA entry holds the golden weights, the model entry garbage: loading with
+    use_ema=True must reproduce the golden score, loading without must not."""
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    name = sorted(cases.SCORE_CASES)[0]
+    cfg, sd, x, labels, out = cases.score_case(name)
+    order = mutils.trainable_parameter_order(cfg)
+    g = torch.Generator().manual_seed(1)
+    ck = {"info": 1, "optimizer": {}, "step": 5,
+          "model": {"module." + k: (v if k not in order else torch.randn(v.shape, generator=g) * 0.05) for k, v in sd.items()},
+          "ema": {"decay": 0.999, "num_updates": 5, "shadow_params": [sd[k] for k in order]}}
+    path = str(tmp_path / "checkpoint_1.pth")
+    torch.save(ck, path)
+    m = mutils.ScoreModel(cfg, device=cuda, precision="fp32", init=False)
+    assert mutils.load_checkpoint(path, m, use_ema=True) is m
+    y = m(x.to(cuda), labels.to(cuda)).cpu()
+    assert cases.max_rel(y, out) < FP32_TOL
+    mutils.load_checkpoint(path, m, use_ema=False)
+    y2 = m(x.to(cuda), labels.to(cuda)).cpu()
+    assert cases.rel_l2(y2, out) > 0.1
