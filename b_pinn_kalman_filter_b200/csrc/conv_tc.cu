@@ -70,7 +70,7 @@ struct TcSmem {
   static constexpr int OUT_BUF = TC_BM * 128 * 2;              // 128 columns per pass (2 passes for BN = 256)
   static constexpr int OUT_BYTES = (BN >= 128) ? OUT_BUF * (DS ? 2 : 1) : 0;
   static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;           // barriers + tmem slot, + slack for 1024 B alignment
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024 + 1024;   // barriers, bias+temb table, alignment slack           // barriers + tmem slot, + slack for 1024 B alignment
 };
 
 // Halo variant (3x3, BN = 128, tile = 8 wide x 16 high pixels of one image).  With one TMA box per tap an N = 128 tile
@@ -95,7 +95,7 @@ struct TcSmem<BN, true, DS> {
   static constexpr int OUT_BUF = TC_BM * 128 * 2;
   static constexpr int OUT_BYTES = OUT_BUF;
   static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024 + 1024;   // barriers, bias+temb table, alignment slack
   static constexpr int STAGE_BYTES = 0;
 };
 
@@ -113,7 +113,7 @@ struct TcSmemPair {
   static constexpr int OUT_BUF = TC_BM * 128 * 2;
   static constexpr int OUT_BYTES = OUT_BUF;
   static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024 + 1024;   // barriers, bias+temb table, alignment slack
 };
 // Pair + halo (Cout tile 128): a single SM's 128 x 128 x 16 MMA reads 4 KB of A and 4 KB of B per 64 clk, i.e. all of
 // the 128 B/clk shared memory delivers; as half of a 256 x 128 pair MMA it reads 4 + 2 KB.  Each CTA loads 64 of the
@@ -133,7 +133,7 @@ struct TcSmemHaloPairT {
   static constexpr int OUT_BUF = TC_BM * 128 * 2;
   static constexpr int OUT_BYTES = OUT_BUF * (DS ? 2 : 1);
   static constexpr int BAR_OFF = OUT_OFF + OUT_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024 + 1024;   // barriers, bias+temb table, alignment slack
   static constexpr int STAGE_BYTES = 0;
 };
 template <int BN, bool HALO, bool DS, bool PAIR> struct TcSmemSel { using type = TcSmem<BN, HALO, DS>; };
@@ -388,10 +388,32 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       if (p.res && threadIdx.x == 64 && tile_first < tile_end) res_fetch(tile_first, 0, 0);
     }
     int pcount = 0;                                      // passes done by this CTA (DS: staging buffer = pcount & 1)
+    // bias[n] + temb[b, n] of the tile's BN columns (tiles inside one image, TB == 1): the 16 broadcast global loads
+    // per 32-column chunk sat on the critical path of every epilogue-bound tile (long-scoreboard stalls on the first
+    // FADDs, profiles/r01g_conv_tc_ncu_full.txt).  One thread per column now fetches the NEXT tile's value while this
+    // tile is drained and drops it into a 1 KB shared table after the last read of the current one.
+    float* btab = reinterpret_cast<float*>(smem_raw + (bar0 - smem_u32(smem_raw)) + 256);
+    const bool use_tab = EPI == 0 && p.TB == 1 && (p.bias || p.temb);
+    const int et_col = (int)threadIdx.x - 64;            // column of the table this thread maintains (< BN)
+    auto tab_value = [&](int tile_) -> float {
+      int mt_, nt_, b0_, h0_, w0_;
+      tile_coords(tile_, mt_, nt_);
+      m_origin(mt_, b0_, h0_, w0_);
+      float v = 0.0f;
+      if (et_col < BN && b0_ < p.B) {
+        if (p.bias) v = __ldg(p.bias + nt_ * BN + et_col);
+        if (p.temb) v += __ldg(p.temb + (size_t)b0_ * p.temb_stride + nt_ * BN + et_col);
+      }
+      return v;
+    };
+    if (use_tab && tile_first < tile_end && et_col < BN) btab[et_col] = tab_value(tile_first);
     for (int tile = tile_first; tile < tile_end; tile += tile_step) {
       int mt, nt, b0, h0, w0;
       tile_coords(tile, mt, nt);
       m_origin(mt, b0, h0, w0);
+      const bool tab_more = use_tab && tile + tile_step < tile_end;
+      float tab_next = 0.0f;
+      if (tab_more) tab_next = tab_value(tile + tile_step);   // in flight while this tile is drained
       const int lw = m_local % p.TW, lh = (m_local / p.TW) % p.TH, lb = m_local / (p.TW * p.TH);
       const int b = b0 + lb, h = h0 + lh, w = w0 + lw;
       const bool valid = b < p.B;
@@ -399,6 +421,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       const float* bs = p.bias ? p.bias + nt * BN : nullptr;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
+      if (use_tab) asm volatile("bar.sync 1, 256;" ::: "memory");   // the table holds this tile's values
       const uint32_t t_addr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BN);
       if constexpr (EPI == 1) {
         uint32_t r[16];
@@ -465,6 +488,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           float v[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          if (use_tab) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 t = *reinterpret_cast<const float4*>(btab + c0 + j);
+              v[j] += t.x; v[j + 1] += t.y; v[j + 2] += t.z; v[j + 3] += t.w;
+            }
+          } else {
           if (bs) {
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
@@ -478,6 +508,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               const float4 t = __ldg(reinterpret_cast<const float4*>(tb + c0 + j));
               v[j] += t.x; v[j + 1] += t.y; v[j + 2] += t.z; v[j + 3] += t.w;
             }
+          }
           }
           if (p.res) {
 #pragma unroll
@@ -513,6 +544,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       }
       fence_proxy_async_smem();                        // generic-proxy smem writes -> visible to the TMA store
       asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (tab_more && pass == BN / 128 - 1 && et_col < BN) btab[et_col] = tab_next;
       if (threadIdx.x == 64) {
         tma_store_4d(base + sofs, &mapOut, nt * BN + pass * 128, w0, h0, b0);
         tma_store_4d(base + sofs + TC_BM * 128, &mapOut, nt * BN + pass * 128 + 64, w0, h0, b0);
