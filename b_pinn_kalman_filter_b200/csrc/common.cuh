@@ -35,7 +35,18 @@ template <> __device__ __forceinline__ bf16 from_f<bf16>(float v) { return __flo
 
 __device__ __forceinline__ float silu(float v) { return v / (1.0f + __expf(-v)); }
 // bf16 paths: MUFU.EX2 + MUFU.RCP (2 ulp) instead of the IEEE division -- the result is rounded to 8 bits anyway
+#ifdef B200_SILU_EXP
 __device__ __forceinline__ float silu_fast(float v) { return __fdividef(v, 1.0f + __expf(-v)); }
+#else
+// x sigmoid(x) = h + h tanh(h), h = x / 2: ONE MUFU op (tanh.approx.f32, relative error 2^-11) instead of EX2 + RCP; the
+// GroupNorm apply pass issues 8 of these per 16 bytes and was at 55-65 % of the MUFU rate of the throttled clock
+__device__ __forceinline__ float silu_fast(float v) {
+  const float h = 0.5f * v;
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(h));
+  return fmaf(h, t, h);
+}
+#endif
 template <typename T> __device__ __forceinline__ float silu_t(float v);
 template <> __device__ __forceinline__ float silu_t<float>(float v) { return silu(v); }
 template <> __device__ __forceinline__ float silu_t<__nv_bfloat16>(float v) { return silu_fast(v); }

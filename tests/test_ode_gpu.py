@@ -143,7 +143,11 @@ def test_dps_sampler_device_solver_matches_scipy_driver(cuda):
     obsv = sde_lib.LOBSVSDE(state, op(truth.to(cuda), keep_shape=False), op)
     config = SimpleNamespace(device=cuda, inverse=SimpleNamespace(variance=0.1, solver="RK45", sampler="dps"))
     torch.manual_seed(0)
-    sampler = cs.get_sampler(config, obsv, shape, eps=0.7)      # short interval: a few dozen RHS evaluations
+    # Short interval: with these weights the guided ODE is stiff (steps of 1e-4 .. 1e-3), so [1, 0.7] took 856 steps and
+    # 5300 right-hand sides per solver; over that many steps one fp64-vs-fp32 rounding of a state entry, amplified by
+    # the bf16 network, eventually flips an accept / reject decision (seen: 5300 vs 5276 evaluations).  [1, 0.99] keeps
+    # the comparison to a few dozen steps, where both drivers make the same decisions.
+    sampler = cs.get_sampler(config, obsv, shape, eps=0.99)
     xd = sampler(m, z=z.clone())
     xs = sampler(m, z=z.clone(), solver="scipy")
     assert xd.shape == shape and torch.isfinite(xd).all()
