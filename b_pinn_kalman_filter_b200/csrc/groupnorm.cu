@@ -22,6 +22,11 @@ struct GnArgs {
   const float* st1; const float* st2; int T1, T2;
 };
 
+template <typename T> struct AccT { using type = float; };
+template <> struct AccT<float> { using type = double; };
+__device__ __forceinline__ float gn_rsqrt(double v) { return (float)(1.0 / sqrt(v)); }
+__device__ __forceinline__ float gn_rsqrt(float v) { return rsqrtf(v); }
+
 // Thread layout shared by both kernels: `nthr` threads sweep pixels; nthr is a multiple of CV = C/8 so that each
 // thread always owns the same 8 channels (cv = tid % CV) and steps over pixels.
 template <typename T>
@@ -82,7 +87,12 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(GnArgs a) {
   const int cpg = C / a.G;
   b200_pdl_wait();
   b200_pdl_trigger();
-  double* chs = reinterpret_cast<double*>(sh + 2 * a.G);      // [C] sums, [C] sums of squares (stats path only)
+  // Statistics are folded in fp64 on the strict fp32 path and in fp32 on the bf16 path: B200's fp64 rate is 1/64 of
+  // fp32, and 2 (T + 1) C double additions + a double division and square root per group cost a block about as many
+  // cycles as streaming its 64 KB share of a 16x16 activation (the sums are over <= 16 K values of O(1): fp32 leaves
+  // ~1e-6 relative error on rstd, two orders below the bf16 rounding of the output).
+  using acc_t = typename AccT<T>::type;
+  acc_t* chs = reinterpret_cast<acc_t*>(sh + 2 * a.G);      // [C] sums, [C] sums of squares (stats path only)
   if (a.st1) {
     // fold the slots per channel with all threads (coalesced over channels), then the channels per group
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -90,30 +100,30 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(GnArgs a) {
       const float* base = first ? a.st1 + ((size_t)b * a.T1 * a.C1 + c) * 2
                                 : a.st2 + ((size_t)b * a.T2 * a.C2 + (c - a.C1)) * 2;
       const int T = first ? a.T1 : a.T2, cs = first ? a.C1 : a.C2;
-      double ts = 0.0, tq = 0.0;
+      acc_t ts = 0, tq = 0;
       for (int k = 0; k < T; ++k) {
         const float2 v = __ldg(reinterpret_cast<const float2*>(base + (size_t)k * cs * 2));
-        ts += (double)v.x; tq += (double)v.y;
+        ts += (acc_t)v.x; tq += (acc_t)v.y;
       }
       chs[c] = ts; chs[C + c] = tq;
     }
     __syncthreads();
   }
   for (int g = threadIdx.x; g < a.G; g += blockDim.x) {
-    double ts = 0.0, tq = 0.0;
+    acc_t ts = 0, tq = 0;
     if (a.st1) {
       for (int c = g * cpg; c < (g + 1) * cpg; ++c) { ts += chs[c]; tq += chs[C + c]; }   // may straddle the sources
     } else
     for (int k = 0; k < a.nsplit; ++k) {
       const float* o = a.partial + (((size_t)b * a.nsplit + k) * a.G + g) * 2;
-      ts += (double)o[0]; tq += (double)o[1];
+      ts += (acc_t)o[0]; tq += (acc_t)o[1];
     }
-    const double n = (double)a.HW * cpg;
-    const double mean = ts / n;
-    double var = tq / n - mean * mean;
-    if (var < 0.0) var = 0.0;
+    const acc_t rn = (acc_t)1 / ((acc_t)a.HW * (acc_t)cpg);
+    const acc_t mean = ts * rn;
+    acc_t var = tq * rn - mean * mean;
+    if (var < (acc_t)0) var = 0;
     sh[g] = (float)mean;
-    sh[a.G + g] = (float)(1.0 / sqrt(var + (double)a.eps));
+    sh[a.G + g] = gn_rsqrt(var + (acc_t)a.eps);
   }
   __syncthreads();
   const int ppt = blockDim.x / CV;
