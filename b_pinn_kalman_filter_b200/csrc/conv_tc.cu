@@ -851,7 +851,12 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   tile_box(B, H, W, p.TW, p.TH, p.TB, p.tiles_w, p.tiles_h);
   p.num_m = p.TB > 1 ? (B + p.TB - 1) / p.TB : B * p.tiles_w * p.tiles_h;
   int BN = out_mode != 0 ? 16 : ((Cout % 256 == 0) ? 256 : 128);
-  if (BN == 256 && p.num_m * (Cout / 256) < B200_NUM_SMS) BN = 128;   // small levels: more, narrower tiles
+  // small levels: more, narrower tiles -- unless the CTA-pair variant still fills most of the 74 SM pairs in ONE wave of
+  // 256 x 256 tiles (4x4 maps at B = 1024: 64 pairs; two waves of 128-wide tiles took twice as long)
+  static const int pair_min = [] { const char* e = getenv("B200_CONV_PAIR_MIN"); return e ? atoi(e) : 48; }();
+  const bool pair_small = out_mode == 0 && ksize == 3 && pair_enabled() &&
+                          ((p.num_m + 1) / 2) * (Cout / 256) >= pair_min;
+  if (BN == 256 && p.num_m * (Cout / 256) < B200_NUM_SMS && !pair_small) BN = 128;
   p.num_n = out_mode != 0 ? 1 : Cout / BN;
   p.narrow = out_mode == 2 ? 8 : 0;
   p.bias = bias; p.temb = temb; p.temb_stride = temb_stride; p.res = (const bf16*)res; p.out_scale = out_scale;
