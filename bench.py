@@ -181,8 +181,13 @@ def aux_measurements(dev, pk):
     from b_pinn_kalman_filter_b200.op import ns_step
     out = {}
 
-    def timeit(fn, iters=10):
-        for _ in range(3):
+    # each kernel is timed ALONE (the roofline's burst HBM figure is measured the same way): let the board come back
+    # from the power-capped clocks of the sampling run before the first one
+    torch.cuda.synchronize()
+    time.sleep(2.0)
+
+    def timeit(fn, iters=20):
+        for _ in range(5):
             fn()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
