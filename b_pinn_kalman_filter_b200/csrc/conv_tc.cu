@@ -119,16 +119,20 @@ struct TcSmemPair {
 // the 128 B/clk shared memory delivers; as half of a 256 x 128 pair MMA it reads 4 + 2 KB.  Each CTA loads 64 of the
 // 128 weight rows per tap (8 KB boxes); a ring stage holds one filter ROW (3 taps, 24 KB), so the single MMA-issuing
 // thread -- whose per-tap barrier traffic is what paces N = 128 tiles -- waits and commits 6 instead of 18 times per tile.
-template <bool DS>
+// BN = 256 (halo + pair): the 256 x 256 pair tile with halo reuse of its activations -- per K block and SM 54 KB of
+// activations serve all nine taps (instead of 9 x 16 KB) next to 9 x 16 KB of weights: 1.18 MB -> 0.81 MB of L2 reads
+// per tile, for the shapes whose MMA issuer still waited 23 % of its time for operand stages.  Per-tap weight ring
+// (four 128-clk MMAs per tap hide the barrier round trip), 5 x 16 KB.
+template <bool DS, int BN = 128>
 struct TcSmemHaloPairT {
   static constexpr int BOX_BYTES = (HALO_TH + 2) * HALO_TW * 128;
   static constexpr int A_BYTES = 3 * BOX_BYTES;
-  static constexpr int B_BYTES = 64 * TC_BK * 2;               // 8 KB
+  static constexpr int B_BYTES = (BN / 2) * TC_BK * 2;         // 8 KB (BN = 128) / 16 KB (BN = 256)
   static constexpr int STAGES = 2;
-  static constexpr int WGROUP = 3;                             // taps per weight-ring stage: one filter row
-  static constexpr int WSTAGES = DS ? 2 : 3;                   // DS: a ring stage makes room for the second staging buffer
+  static constexpr int WGROUP = BN == 128 ? 3 : 1;             // taps per weight-ring stage: one filter row (BN = 128)
+  static constexpr int WSTAGES = BN == 128 ? (DS ? 2 : 3) : 5; // DS: a ring stage makes room for the second staging buffer
   static constexpr int W_OFF = STAGES * A_BYTES;
-  static constexpr int TMEM_COLS = 256;
+  static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int OUT_OFF = W_OFF + WSTAGES * WGROUP * B_BYTES;
   static constexpr int OUT_BUF = TC_BM * 128 * 2;
   static constexpr int OUT_BYTES = OUT_BUF * (DS ? 2 : 1);
@@ -138,7 +142,7 @@ struct TcSmemHaloPairT {
 };
 template <int BN, bool HALO, bool DS, bool PAIR> struct TcSmemSel { using type = TcSmem<BN, HALO, DS>; };
 template <int BN, bool DS> struct TcSmemSel<BN, false, DS, true> { using type = TcSmemPair; };
-template <int BN, bool DS> struct TcSmemSel<BN, true, DS, true> { using type = TcSmemHaloPairT<DS>; };
+template <int BN, bool DS> struct TcSmemSel<BN, true, DS, true> { using type = TcSmemHaloPairT<DS, BN>; };
 using TcSmemHaloPair = TcSmemHaloPairT<false>;
 
 template <int BN, int EPI, bool HALO = false, bool DS = false, bool PAIR = false>
@@ -147,9 +151,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
                const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapOut,
                const __grid_constant__ CUtensorMap mapRes, const ConvTcParams p) {
   using S = typename TcSmemSel<BN, HALO, DS, PAIR>::type;
-  static_assert(!PAIR || (EPI == 0 && ((BN == 256 && !HALO && !DS) || (BN == 128 && HALO))), "pair variants");
+  static_assert(!PAIR || (EPI == 0 && ((BN == 256 && !DS) || (BN == 128 && HALO))), "pair variants");
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
-  constexpr int NWS = HALO ? (PAIR ? TcSmemHaloPairT<DS>::WSTAGES : TcSmem<BN, true>::WSTAGES) : 0;   // weight ring (halo)
+  constexpr int NWS = HALO ? (PAIR ? TcSmemHaloPairT<DS, BN>::WSTAGES : TcSmem<BN, true>::WSTAGES) : 0;   // weight ring (halo)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t bar0 = base + S::BAR_OFF;
@@ -872,7 +876,9 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   if (rc) return rc;
   if (out_mode != 0) return launch<16, 1>(a1, a2, wm, a1, p, st);
   CUtensorMap om;
-  if (BN == 128 && ksize == 3 && p.TB == 1 && H % HALO_TH == 0 && W % HALO_TW == 0 && halo_enabled()) {
+  static const bool hp256 = [] { const char* e = getenv("B200_CONV_HALO_PAIR256"); return !(e && e[0] == '0'); }();
+  const bool halo256 = BN == 256 && hp256 && halo_pair_enabled() && pair_enabled();
+  if ((BN == 128 || halo256) && ksize == 3 && p.TB == 1 && H % HALO_TH == 0 && W % HALO_TW == 0 && halo_enabled()) {
     // N = 128 tiles are bound by activation ingress, not by the tensor pipe: 8 x 16 pixel tiles with halo reuse
     p.TW = HALO_TW; p.TH = HALO_TH; p.tiles_w = W / HALO_TW; p.tiles_h = H / HALO_TH;
     p.num_m = B * p.tiles_w * p.tiles_h;
@@ -883,6 +889,12 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
     else a2 = a1;
     rc = act_map(&om, out, B, H, W, Cout, HALO_TW, HALO_TH, 1);
     if (rc) return rc;
+    if (BN == 256) {
+      CUtensorMap wh;                                     // each CTA of the pair loads 128 of the 256 weight rows
+      rc = weight_map(&wh, w, Cout, Ktot, 128);
+      if (rc) return rc;
+      return launch_pair<256, true>(a1, a2, wh, om, p, st);
+    }
     if (halo_pair_enabled()) {
       CUtensorMap wh;                                     // each CTA of the pair loads 64 of the 128 weight rows
       rc = weight_map(&wh, w, Cout, Ktot, 64);
