@@ -168,7 +168,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   const uint32_t tmem_slot = res_bar + 8u;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // the warp index through a shuffle: provably warp-uniform, so the role branches below are convergent for ptxas
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const int Ctot = p.C1 + p.C2;
   const int kb_per_tap = Ctot / TC_BK;
   const int taps = p.taps_w * p.taps_w;
@@ -219,7 +220,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
 
   if (warp == 0) {
     // ================= TMA producer =================
-    if (lane == 0) {
+    {  // the whole warp runs the loop and waits; one elected lane issues (keeps descriptors in uniform registers)
+      const bool elected = tc_elect_one();
       int stage = 0; uint32_t phase = 0;
       for (int tile = tile_first; tile < tile_end; tile += tile_step) {
         int mt, nt, b0, h0, w0;
@@ -229,6 +231,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           // activations only: three column-shifted boxes with one halo row above and below per 64-channel block
           for (int kb = 0; kb < kb_per_tap; ++kb) {
             mbar_wait(empty_bar(stage), phase ^ 1);
+            if (elected) {
             const uint32_t sa = base + stage * S::A_BYTES;
             const int c = kb * TC_BK;
             if constexpr (PAIR) {
@@ -247,6 +250,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               else tma_load_4d(sa + sx * S::BOX_BYTES, &mapA2, full_bar(stage), c - p.C1, w0 + sx - 1, h0 - 1, b0);
             }
             }
+            }
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
         } else {
@@ -254,6 +258,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           const int r = tap / p.taps_w, s = tap - r * p.taps_w;
           for (int kb = 0; kb < kb_per_tap; ++kb) {
             mbar_wait(empty_bar(stage), phase ^ 1);
+            if (elected) {
             const uint32_t sa = base + stage * S::STAGE_BYTES, sb = sa + S::A_BYTES;
             const int c = kb * TC_BK;
             if constexpr (PAIR) {
@@ -269,6 +274,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             else tma_load_4d(sa, &mapA2, full_bar(stage), c - p.C1, w0 * p.stride + s - p.pad, h0 * p.stride + r - p.pad, b0);
             tma_load_2d(sb, &mapW, full_bar(stage), tap * Ctot + c, nt * BN);
             }
+            }
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
         }
@@ -278,7 +284,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   } else if (HALO && warp == 10) {
     // ================= weight producer (halo variant): one [BN x 64] box per (K block, tap) =================
     if constexpr (HALO) {
-      if (lane == 0) {
+      {
+        const bool elected = tc_elect_one();
         int ws = 0; uint32_t wphase = 0;
         for (int tile = tile_first; tile < tile_end; tile += tile_step) {
           int mt, nt;
@@ -286,6 +293,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           for (int kb = 0; kb < kb_per_tap; ++kb)
             for (int tap = 0; tap < 9; tap += S::WGROUP) {
               mbar_wait(wempty_bar(ws), wphase ^ 1);
+              if (elected) {
               const uint32_t wdst = base + S::W_OFF + ws * (S::WGROUP * S::B_BYTES);
               if constexpr (PAIR) {
                 const uint32_t lbar = mapa_cta(wfull_bar(ws), 0);
@@ -300,6 +308,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               for (int g = 0; g < S::WGROUP; ++g)
                 tma_load_2d(wdst + g * S::B_BYTES, &mapW, wfull_bar(ws), (tap + g) * Ctot + kb * TC_BK, nt * BN);
               }
+              }
               if (++ws == NWS) { ws = 0; wphase ^= 1; }
             }
         }
@@ -307,7 +316,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    if (lane == 0 && cta_rank == 0) {
+    // The WHOLE warp runs the loop (waits included) and one elected lane issues: inside an `if (lane == 0)` region
+    // ptxas cannot keep the descriptors in uniform registers and wraps every UTCHMMA in an ELECT / 6 x R2UR.BROADCAST /
+    // BRA.U.ANY "waterfall" -- ~86 clk per issued MMA against the 64 clk an N = 128 MMA takes to execute.
+    if (cta_rank == 0) {
+      const bool elected = tc_elect_one();
+      const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
       // instruction descriptor: D = f32, A = B = bf16, both K-major, N = BN, M = 128 (PAIR: 256 over the two CTAs)
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) |
                              ((uint32_t)((PAIR ? 2 * TC_BM : TC_BM) >> 4) << 24);
@@ -318,7 +332,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       for (int tile = tile_first; tile < tile_end; tile += tile_step) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        const uint32_t d_tmem = tmem_u + (uint32_t)(acc * BN);
         if constexpr (HALO) {
           for (int kb = 0; kb < kb_per_tap; ++kb) {
             mbar_wait(full_bar(stage), phase);
@@ -330,6 +344,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               mbar_wait(wfull_bar(ws), wphase);
               tc_fence_after();
               const uint64_t db0 = make_sw128_desc(base + S::W_OFF + ws * (S::WGROUP * S::B_BYTES));
+              if (elected) {
 #pragma unroll
               for (int g = 0; g < S::WGROUP; ++g) {
                 const int tap = tap0 + g, r = tap / 3, sx = tap - r * 3;
@@ -343,9 +358,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
                 }
               }
               if constexpr (PAIR) tc_commit_2sm(wempty_bar(ws)); else tc_commit(wempty_bar(ws));
+              }
               if (++ws == NWS) { ws = 0; wphase ^= 1; }
             }
-            if constexpr (PAIR) tc_commit_2sm(empty_bar(stage)); else tc_commit(empty_bar(stage));
+            if (elected) { if constexpr (PAIR) tc_commit_2sm(empty_bar(stage)); else tc_commit(empty_bar(stage)); }
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
         } else {
@@ -354,6 +370,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           tc_fence_after();
           const uint32_t sa = base + stage * S::STAGE_BYTES, sb = sa + S::A_BYTES;
           const uint64_t da = make_sw128_desc(sa), db = make_sw128_desc(sb);
+          if (elected) {
 #pragma unroll
           for (int k = 0; k < TC_BK / 16; ++k) {
             // advance 16 elements (32 B) along K inside the 128 B swizzle row: +2 in the 16-byte-unit address field
@@ -361,10 +378,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             else tc_mma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
           }
           if constexpr (PAIR) tc_commit_2sm(empty_bar(stage)); else tc_commit(empty_bar(stage));
+          }
           if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
         }
-        if constexpr (PAIR) tc_commit_2sm(tfull_bar(acc)); else tc_commit(tfull_bar(acc));
+        if (elected) { if constexpr (PAIR) tc_commit_2sm(tfull_bar(acc)); else tc_commit(tfull_bar(acc)); }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
