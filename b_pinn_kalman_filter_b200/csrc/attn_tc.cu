@@ -188,8 +188,8 @@ extern "C" int b200_attention_tc(const void* qkv, void* out, int B, int L, int C
   if (!qkv || !out || B < 0) return B200_ERR_ARG;
   if (!b200_attention_tc_supported(L, C)) return B200_ERR_UNSUPPORTED;
   if (B == 0) return B200_OK;
-  static cudaError_t attr_err = cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
-  if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
+  static int attr_state[B200_MAX_DEVICES];
+  if (int rc = b200_set_smem_once(attr_state, attn_tc_kernel, AT_SMEM)) return rc;
   CUtensorMap map;
   const uint64_t dims[3] = {(uint64_t)3 * C, (uint64_t)L, (uint64_t)B};
   const uint64_t strides[2] = {(uint64_t)3 * C * 2, (uint64_t)L * 3 * C * 2};

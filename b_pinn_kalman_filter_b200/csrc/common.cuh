@@ -135,6 +135,22 @@ struct Philox {
 
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a PER-DEVICE property of a kernel: set it once per (kernel
+// instantiation, device ordinal), not once per process -- a second engine on another GPU of the same process would
+// otherwise fail its large-shared-memory launches.  `state` is the caller's static array (zero-initialised);
+// entries: 0 = not set, 1 = set, < 0 = -(1000 + cudaError).  Racing threads both set the attribute (idempotent).
+#define B200_MAX_DEVICES 64
+template <typename K>
+inline int b200_set_smem_once(int* state, K kern, int bytes) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= B200_MAX_DEVICES) return B200_ERR_ARG;
+  if (state[dev] == 0) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    state[dev] = e == cudaSuccess ? 1 : -(1000 + (int)e);
+  }
+  return state[dev] == 1 ? B200_OK : state[dev];
+}
+
 
 // ---- programmatic dependent launch ------------------------------------------------------------------------------------
 // A kernel launched through b200_launch_pdl may be scheduled while its predecessor in the stream is still draining

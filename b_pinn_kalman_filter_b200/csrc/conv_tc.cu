@@ -743,13 +743,8 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
     const int rc = act_map(&rm, p.res, p.B, p.H, p.W, p.Cout, p.TW, p.TH, p.TB);
     if (rc) return rc;
   }
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_tc_kernel<BN, EPI, HALO, DS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    TcSmem<BN, HALO, DS>::TOTAL);
-  });
-  if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
+  static int attr_state[B200_MAX_DEVICES];
+  if (int rc = b200_set_smem_once(attr_state, conv_tc_kernel<BN, EPI, HALO, DS>, TcSmem<BN, HALO, DS>::TOTAL)) return rc;
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
   cudaError_t le = b200_launch_pdl(conv_tc_kernel<BN, EPI, HALO, DS>, dim3(grid), dim3(TC_THREADS + (HALO ? 32 : 0)),
@@ -762,13 +757,9 @@ template <int BN, bool HALO, bool DS = false>
 int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
                 const ConvTcParams& p, cudaStream_t st) {
   using SP = typename TcSmemSel<BN, HALO, DS, true>::type;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
+  static int attr_state[B200_MAX_DEVICES];
   auto kern = conv_tc_kernel<BN, 0, HALO, DS, true>;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SP::TOTAL);
-  });
-  if (attr_err != cudaSuccess) return -(1000 + (int)attr_err);
+  if (int rc = b200_set_smem_once(attr_state, kern, SP::TOTAL)) return rc;
   CUtensorMap rm = om;
   if (p.res) {
     const int rc = act_map(&rm, p.res, p.B, p.H, p.W, p.Cout, p.TW, p.TH, p.TB);

@@ -502,6 +502,11 @@ class ScoreEngine:
                 self.uniform_mode = uniform and not grad
                 try:
                     b = Builder(self, B, dry=False)
+                    if grad:
+                        # the retained activations of a grad plan must survive whatever other plan runs between
+                        # forward_for_grad and input_grad (a `model(x, t)` call, a PC step): private buffers, not the
+                        # engine-wide free list that every other plan is packed into
+                        b.ws = Workspace(self.device)
                     self.net_builder(b, self.config)
                     b.plan.n_fwd = len(b.plan.ops)
                     if grad:

@@ -38,6 +38,10 @@ def build_ncsnpp(b, config):
         # needs Upsample(fir=True, with_conv=True) -> upsample_conv_2d, which raises in the reference itself
         # (models/up_or_down_sampling.py:126) and is used by no shipped config.
         raise NotImplementedError("progressive='residual' is unreachable in the reference (upsample_conv_2d is broken)")
+    if not fir and (progressive != "none" or progressive_input != "none"):
+        # the reference's pyramid resamplers follow `fir` (Down/Upsample(fir=fir, with_conv=False), ncsnpp.py:101, 110:
+        # avg_pool2d / nearest when fir=False); only the FIR form is built here and no shipped config needs the other
+        raise NotImplementedError("progressive pyramids with fir=False (avg-pool / nearest resamplers): no shipped config")
     if combine != "sum" and progressive_input == "input_skip":
         raise NotImplementedError("progressive_combine='cat' is used by no shipped config")
 

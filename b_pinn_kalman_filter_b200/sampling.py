@@ -29,12 +29,31 @@ _PREDICTORS = {}
 
 # Optional noise source for parity tests: callable(shape, device) -> fp32 tensor; None = fused Philox on device.
 NOISE_FN = None
-# Philox stream id source for the fused generator.
+# Fused generator: Philox4x32-10 keyed by `_SEED`, counter = (element group, stream id).  Stream ids are handed out by
+# ONE process-wide counter: every update of the generic path takes one, every fused loop reserves a block of
+# 16 * (N + 1) (update k of device step i draws stream base + 16 i + k), and the device-side prior takes one -- so no two
+# draws under one seed ever share a stream, and successive `pc_sampler(model)` calls see fresh noise the way successive
+# `torch.randn_like` calls do in the reference (sampling.py:197, 275).  `set_seed` rewinds the counter (reproducible runs).
 _SEED = [0x5DEECE66D]
+_STREAM = [0]
+STREAMS_PER_STEP = 16      # csrc/sde_update.cu B200_OFFSETS_PER_STEP
 
 
 def set_seed(seed):
     _SEED[0] = int(seed) & 0xFFFFFFFFFFFFFFFF
+    _STREAM[0] = 0
+
+
+def reserve_streams(n):
+    """First id of a fresh block of `n` Philox stream ids."""
+    base = _STREAM[0] + 1
+    _STREAM[0] += int(n)
+    return base
+
+
+# Shard context of the generic (user-subclass) path: set by pc_sampler around its loop so that `_apply` /
+# `langevin_update` draw the GLOBAL batch's noise field and all-reduce the Langevin norms like the fused loop does.
+_SHARD = {"elem_base": 0, "group": None, "total_batch": None}
 
 
 def _register(table, kind):
@@ -106,12 +125,8 @@ def fused_update(x, score, a, b, c, z=None, seed=None, offset=0, elem_base=0):
     return xn, xm
 
 
-_OFFSET = [0]
-
-
 def _next_offset():
-    _OFFSET[0] += 1
-    return _OFFSET[0]
+    return reserve_streams(1)
 
 
 def _index(sde, t):
@@ -149,7 +164,7 @@ class Corrector(abc.ABC):
 
 def _apply(x, score, a, b, c):
     z = _noise(x.shape, x.device)
-    return fused_update(x, score, a, b, c, z=z, offset=_next_offset())
+    return fused_update(x, score, a, b, c, z=z, offset=_next_offset(), elem_base=_SHARD["elem_base"])
 
 
 @register_predictor(name='euler_maruyama')
@@ -267,13 +282,15 @@ class LangevinCorrector(Corrector):
         x_mean = x
         for _ in range(self.n_steps):
             grad = self.score_fn(x, t)
-            x, x_mean = langevin_update(x, grad, alpha, self.snr)
+            x, x_mean = langevin_update(x, grad, alpha, self.snr, process_group=_SHARD["group"],
+                                        total_batch=_SHARD["total_batch"], elem_base=_SHARD["elem_base"])
         return x, x_mean
 
 
-def langevin_update(x, grad, alpha, snr, z=None, process_group=None):
+def langevin_update(x, grad, alpha, snr, z=None, process_group=None, total_batch=None, elem_base=0):
     """One fused Langevin step (norm pass + update pass).  With a process group the two batch-mean norms are
-    all-reduced so that sharded batches reproduce the single-device step size exactly."""
+    all-reduced so that sharded batches reproduce the single-device step size exactly; `total_batch` is then the
+    GLOBAL batch the means are taken over (shards may be ragged) and `elem_base` this shard's first global element."""
     _lib.require_cuda(x, grad)
     lib = _lib.lib()
     B = x.shape[0]
@@ -289,19 +306,21 @@ def langevin_update(x, grad, alpha, snr, z=None, process_group=None):
     sums = torch.empty(2, device=dev, dtype=torch.float32)
     seed, off = _SEED[0], _next_offset()
     total = B
+    if process_group is not None:
+        if total_batch is None:
+            raise ValueError("langevin_update: a process group needs total_batch (the global batch the norms average over)")
+        total = int(total_batch)
     with torch.cuda.device(dev):
         st = _lib.stream()
         _lib.check(lib.b200_sample_sumsq(_lib.ptr(ss[0]), _lib.ptr(ss[1]), _lib.ptr(g), _lib.ptr(z), B, n_per, seed, off,
-                                         0, None, st), "b200_sample_sumsq")
+                                         elem_base, None, st), "b200_sample_sumsq")
         _lib.check(lib.b200_langevin_norm_sums(_lib.ptr(sums), _lib.ptr(ss[0]), _lib.ptr(ss[1]), B, st),
                    "b200_langevin_norm_sums")
         if process_group is not None:
-            import torch.distributed as dist
             sharding.allreduce_norm_sums(sums, process_group)
-            total = B * dist.get_world_size(process_group)
         _lib.check(lib.b200_sde_update(_lib.ptr(xn), _lib.ptr(xm), _lib.ptr(g), _lib.ptr(z), _lib.ptr(al), None, None,
-                                       None, 1, _lib.ptr(sums), 1.0 / total, float(snr), B, n_per, seed, off, 0, st),
-                   "b200_sde_update")
+                                       None, 1, _lib.ptr(sums), 1.0 / total, float(snr), B, n_per, seed, off, elem_base,
+                                       st), "b200_sde_update")
     return xn, xm
 
 
@@ -393,6 +412,9 @@ class FusedPCLoop:
         self.dev = eng.device
         self.lib = _lib.lib()
         self.pg = process_group
+        if process_group is not None and total_batch is None:
+            raise ValueError("FusedPCLoop: a process group needs total_batch (the global batch the Langevin norms "
+                             "average over; shards may be ragged)")
         self.total_batch = total_batch or self.B
         self.elem_base = sharding.philox_element_base(rank_offset, self.n_per)
         self.seed = _SEED[0] if seed is None else seed
@@ -406,9 +428,8 @@ class FusedPCLoop:
         # predictor tables
         self.pred = None
         if predictor is not None and predictor is not NonePredictor:
-            pobj = predictor.__new__(predictor)
-            pobj.sde = sde
-            pobj.rsde = type("R", (), {"N": N, "probability_flow": probability_flow})()
+            # the class's own constructor runs its checks (ancestral sampling: VP / VE only, no probability flow)
+            pobj = predictor(sde, None, probability_flow)
             a, b, c = pobj.coefficients(t)
             self.pred = [v.to(torch.float32).contiguous() for v in (a.expand_as(t) if a.dim() else a.repeat(N),
                                                                    b * mult, c)]
@@ -416,6 +437,7 @@ class FusedPCLoop:
         self.corr = None
         self.n_steps = n_steps
         if corrector is not None and corrector is not NoneCorrector and n_steps > 0:
+            corrector(sde, None, snr, n_steps)          # constructor checks (supported SDE classes)
             alpha = _alpha(sde, t).to(torch.float32)
             if corrector is LangevinCorrector:
                 self.corr = ("langevin", alpha.contiguous())
@@ -442,7 +464,7 @@ class FusedPCLoop:
         self.scaled = torch.zeros_like(self.x) if (self.corr and self.corr[0] == "langevin" and
                                                    not bool((mult == 1).all())) else None
         self.graph = None
-        self.offset_base = 0
+        self.offset_base = reserve_streams(STREAMS_PER_STEP * (N + 1))
         self.launches_per_step = 0
         self.forwards_per_step = (n_steps if self.corr else 0) + (1 if self.pred else 0)
 
@@ -508,15 +530,32 @@ class FusedPCLoop:
         return n + 1
 
     # -- API --
-    def reset(self, x0=None):
+    def reset(self, x0=None, fresh_noise=True):
+        """Rewinds the schedule to step 0.  fresh_noise: the next trajectory draws from a NEW block of Philox streams
+        (the stream base is a launch argument, so a captured graph is dropped and re-captured); False replays the
+        noise of the previous trajectory (A/B comparisons)."""
         self.step_dev.zero_()
         self.step_host = 0
+        if fresh_noise and getattr(self, "_used", False):
+            self.offset_base = reserve_streams(STREAMS_PER_STEP * (self.sde.N + 1))
+            self.graph = None
+        self._used = False
         if x0 is not None:
             self.x.copy_(x0)
+
+    def prior_on_device(self, scale):
+        """x_T ~ N(0, scale^2) for THIS shard of the global batch, drawn by b200_fill_normal from the loop's last
+        reserved stream at the shard's global element offset: ranks of a sharded run start from disjoint slices of
+        one noise field whatever their host RNG state (the reference's `sde.prior_sampling` is the host RNG)."""
+        off = self.offset_base + STREAMS_PER_STEP * self.sde.N
+        with torch.cuda.device(self.dev):
+            _lib.check(self.lib.b200_fill_normal(_lib.ptr(self.x), self.x.numel(), float(scale), self.seed, off,
+                                                 self.elem_base, _lib.stream()), "b200_fill_normal")
 
     def step(self):
         """One PC step launched eagerly on the current stream."""
         n = self._step_body(_lib.stream())
+        self._used = True
         self.step_host += 1
         self.launches_per_step = n
         return n
@@ -544,6 +583,7 @@ class FusedPCLoop:
             self.graph = g
         for _ in range(n_iters):
             self.graph.replay()
+        self._used = True
         self.step_host += n_iters
         return (n_iters + 1) * self.launches_per_step
 
@@ -551,7 +591,7 @@ class FusedPCLoop:
 def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
                    n_steps=1, probability_flow=False, continuous=False,
                    denoise=True, eps=1e-3, device='cuda', process_group=None, rank_offset=0, total_batch=None,
-                   gather_output=False):
+                   gather_output=False, prior='auto', seed=None):
     """Create a Predictor-Corrector (PC) sampler (sampling.py:355-411).
 
     Beyond the reference's arguments: `process_group` / `rank_offset` / `total_batch` describe a batch-sharded run
@@ -559,6 +599,11 @@ def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
     the Philox streams) and the Langevin batch-mean norms are all-reduced over the group so that the step size is the
     one the unsharded batch would get (sampling.py:276-278).  `gather_output=True` returns the samples of the whole
     group, concatenated in rank order, on every rank (the one data-path collective of the sharded run).
+    `prior`: 'host' draws x_T with `sde.prior_sampling(shape)` (the host RNG, as the reference does, sampling.py:400) and
+    copies it in; 'device' draws it on the GPU from the Philox stream at the shard's global element offset, so ranks that
+    share a host seed still start from different x_T; 'auto' = 'host' unsharded, 'device' with a process group.
+    `seed`: Philox key of this sampler's noise (default: the module seed, `set_seed`).  Every call of the returned
+    sampler draws from fresh streams.
 
     Returns `pc_sampler(model) -> (samples, nfe)` with nfe = sde.N * (n_steps + 1) exactly as the reference reports
     it (sampling.py:409).
@@ -574,11 +619,18 @@ def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
                 and (corrector is None or corrector in _BUILTIN_CORRECTORS)
                 and isinstance(sde, (sde_lib.VPSDE, sde_lib.subVPSDE, sde_lib.VESDE)))
 
-    def prior(dev):
+    if prior not in ('auto', 'host', 'device'):
+        raise ValueError("get_pc_sampler: prior must be 'auto', 'host' or 'device' (got %r)" % (prior,))
+    if process_group is not None and total_batch is None:
+        raise ValueError("get_pc_sampler: a process group needs total_batch (the global batch size)")
+    device_prior = prior == 'device' or (prior == 'auto' and process_group is not None)
+    prior_scale = sde.sigma_max if isinstance(sde, sde_lib.VESDE) else 1.0
+    n_per = int(np.prod(shape[1:]))
+
+    def host_prior(dev):
         z = _noise(shape, dev)
         if z is not None:
-            scale = sde.sigma_max if isinstance(sde, sde_lib.VESDE) else 1.0
-            return z * scale
+            return z * prior_scale
         return sde.prior_sampling(shape).to(dev)
 
     def pc_sampler(model):
@@ -587,25 +639,42 @@ def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
             if fusable(model):
                 loop = FusedPCLoop(model, sde, shape, predictor, corrector, snr, n_steps, probability_flow,
                                    continuous, eps, process_group=process_group, rank_offset=rank_offset,
-                                   total_batch=total_batch)
+                                   total_batch=total_batch, seed=seed)
                 with torch.cuda.device(dev):
-                    loop.reset(prior(dev))
+                    if device_prior and NOISE_FN is None:
+                        loop.reset()
+                        loop.prior_on_device(prior_scale)
+                    else:
+                        loop.reset(host_prior(dev))
                     loop.run(sde.N)
-                    x = loop.x_mean if denoise else loop.x
-                    if loop.forwards_per_step == 0:
-                        x = loop.x
+                    # NonePredictor returns (x, x): the loop's last x_mean is then the post-corrector NOISY x
+                    # (sampling.py:242-250, 407-409)
+                    x = loop.x if loop.pred is None else (loop.x_mean if denoise else loop.x)
                     x = x.clone()
                     if gather_output:
                         x = sharding.gather_samples(x, process_group, total_batch)
                     return inverse_scaler(x), sde.N * (n_steps + 1)
             # generic path: user-defined predictor/corrector classes around the engine
-            x = prior(dev)
+            elem_base = sharding.philox_element_base(rank_offset, n_per)
+            if device_prior and NOISE_FN is None:
+                x = torch.empty(shape, device=dev, dtype=torch.float32)
+                with torch.cuda.device(dev):
+                    _lib.check(_lib.lib().b200_fill_normal(_lib.ptr(x), x.numel(), float(prior_scale),
+                                                           _SEED[0] if seed is None else seed, _next_offset(),
+                                                           elem_base, _lib.stream()), "b200_fill_normal")
+            else:
+                x = host_prior(dev)
             timesteps = torch.linspace(sde.T, eps, sde.N, device=dev)
             x_mean = x
-            for i in range(sde.N):
-                vec_t = torch.ones(shape[0], device=dev) * timesteps[i]
-                x, x_mean = corrector_update_fn(x, vec_t, model=model)
-                x, x_mean = predictor_update_fn(x, vec_t, model=model)
+            saved = dict(_SHARD)
+            _SHARD.update(elem_base=elem_base, group=process_group, total_batch=total_batch)
+            try:
+                for i in range(sde.N):
+                    vec_t = torch.ones(shape[0], device=dev) * timesteps[i]
+                    x, x_mean = corrector_update_fn(x, vec_t, model=model)
+                    x, x_mean = predictor_update_fn(x, vec_t, model=model)
+            finally:
+                _SHARD.update(saved)
             x = x_mean if denoise else x
             if gather_output:
                 x = sharding.gather_samples(x, process_group, total_batch)

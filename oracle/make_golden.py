@@ -35,6 +35,8 @@ SCORE_CASES = {
     # torch >= 2 rejects (models/layerspp.py:117).
     "cifar10_ncsnpp_ve": ("ve/cifar10_ncsnpp_continuous", "configs.ve.cifar10_ncsnpp_continuous", {}, 2),
     "nc_ddpm_vp": ("vp/nc_ddpmpp", "configs.vp.nc_ddpmpp", {}, 1),
+    # full-size C5 (256x256, output_skip / input_skip pyramids, ncsnpp.py:289-292, 340-346), one image
+    "celebahq256_ncsnpp_ve": ("ve/celebahq_256_ncsnpp_continuous", "configs.ve.celebahq_256_ncsnpp_continuous", {}, 1),
 }
 TINY = dict(nf=32, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=(8,))
 
@@ -106,6 +108,37 @@ def gen_score(ns, name):
     print("score", name, "out rms", float(y.pow(2).mean().sqrt()))
 
 
+def gen_score64(ns, name):
+    """The fp64 arbiter of SURVEY 7.3-H1: the UNMODIFIED reference network in double precision on the inputs and weights
+    of score_<name>.npz (fp32 values, promoted).  err(ours, fp64) is judged against err(reference fp32, fp64)."""
+    our, refm, over, B = SCORE_CASES[name]
+    cfg, rcfg = tiny_pair(our, refm, over)
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    sd = weights.trained_like_state_dict(spec, cfg, seed=1234)
+    model = ns.mutils.create_model(rcfg)
+    model.load_state_dict({"module." + k: v for k, v in sd.items()})
+    model = model.double().eval()
+    g = torch.Generator().manual_seed(99)
+    S, C = cfg.data.image_size, cfg.data.num_channels
+    x = torch.rand(B, C, S, S, generator=g) * 1.5 - 0.25
+    lab = labels_for(cfg, B)
+    # harness shim (the reference is not edited): its FIR taps are built as fp32 tensors (up_or_down_sampling.py:221,
+    # 254) and F.conv2d refuses mixed dtypes; the taps (1,3,3,1)^2/64 are exact in fp32, so promoting them is exact
+    # and its sinusoidal embedding is computed through `.float()` (layers.py:500-514): promoted after the fact
+    orig = ns.updown.upfirdn2d
+    orig_emb = ns.layers.get_timestep_embedding
+    ns.updown.upfirdn2d = lambda inp, kernel, *a, **kw: orig(inp, kernel.to(inp.dtype), *a, **kw)
+    ns.layers.get_timestep_embedding = lambda *a, **kw: orig_emb(*a, **kw).double()
+    try:
+        with torch.no_grad():
+            y = model(x.double(), lab.double())
+    finally:
+        ns.updown.upfirdn2d = orig
+        ns.layers.get_timestep_embedding = orig_emb
+    np.savez_compressed(os.path.join(GOLDEN, "score64_%s.npz" % name), out64=y.numpy())
+    print("score64", name, "out rms", float(y.pow(2).mean().sqrt()))
+
+
 VJP_CASES = ["nc_ddpm_vp", "tiny_fourier_residual", "tiny_output_skip", "tiny_positional_vp"]     # input-gradient (DPS, inverse/conditional_sampling.py:116-136) of the C1/C4 network
 
 
@@ -130,8 +163,9 @@ def gen_vjp(ns, name):
     print("vjp", name, "gx rms", float(gx.pow(2).mean().sqrt()))
 
 
+_POS = {"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}
 PC_CASES = {
-    # name: (overrides, sde, predictor, corrector, snr, n_steps, continuous, N)
+    # name: (overrides, sde, predictor, corrector, snr, n_steps, continuous, N[, extra: net / pf])
     "ve_rd_langevin": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 12),
     "ve_ancestral_ald": ({}, "vesde", "ancestral_sampling", "ald", 0.16, 2, True, 8),
     "vp_em_none": ({"embedding_type": "positional", "scale_by_sigma": False, "_centered": True}, "vpsde",
@@ -145,12 +179,31 @@ PC_CASES = {
                       "reverse_diffusion", "none", 0.1, 1, True, 8),
     # north_star's "fixed-seed 1000-step trajectory": the whole schedule, 2000 network evaluations
     "ve_rd_langevin_1000": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 1000),
+    # the FULL C3 network (nf = 128: every conv on the tensor-core kernels) through 50 PC steps = 100 forwards
+    "c3_ve_rd_langevin": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 50,
+                          {"net": ("ve/cifar10_ncsnpp_continuous", "configs.ve.cifar10_ncsnpp_continuous")}),
+    # VPSDE.discretize (sde_lib.py:191-199) under reverse_diffusion; beta_max = 5 keeps the N = 10 betas < 1
+    "vp_rd_none": (dict(_POS, beta_max=5.0), "vpsde", "reverse_diffusion", "none", 0.16, 1, True, 10),
+    # NonePredictor returns (x, x): the sampler's final x_mean is the post-corrector NOISY x (sampling.py:242-250, 409)
+    "ve_none_langevin": ({}, "vesde", "none", "langevin", 0.16, 1, True, 8),
+    "ve_em_none": ({}, "vesde", "euler_maruyama", "none", 0.16, 1, True, 10),
+    "subvp_em_none": (_POS, "subvpsde", "euler_maruyama", "none", 0.16, 1, True, 10),
+    "vp_rd_probflow": (dict(_POS, beta_max=5.0), "vpsde", "reverse_diffusion", "none", 0.16, 1, True, 10, {"pf": True}),
+    # (euler_maruyama + probability_flow=True raises in the reference itself: RSDE.sde returns the float 0. as
+    # diffusion and sampling.py:186 subscripts it -- no anchor for that combination)
 }
 
 
+def pc_fields(name):
+    t = PC_CASES[name]
+    extra = t[8] if len(t) > 8 else {}
+    return t[:8] + (extra,)
+
+
 def gen_pc(ns, name):
-    over, sde_name, pred, corr, snr, n_steps, continuous, N = PC_CASES[name]
-    cfg, rcfg = tiny_pair("test/tiny_ncsnpp", "configs.ve.cifar10_ncsnpp_continuous", over)
+    over, sde_name, pred, corr, snr, n_steps, continuous, N, extra = pc_fields(name)
+    net = extra.get("net", ("test/tiny_ncsnpp", "configs.ve.cifar10_ncsnpp_continuous"))
+    cfg, rcfg = tiny_pair(net[0], net[1], over)
     for c in (cfg, rcfg):
         c.training.sde = sde_name
         c.training.continuous = continuous
@@ -173,7 +226,7 @@ def gen_pc(ns, name):
         torch.randn_like = lambda t, **kw: next(stream).to(t.dtype)
         type(sde).prior_sampling = lambda self, shp: next(stream) * scale
         fn = ns.sampling.get_pc_sampler(sde, shape, ns.sampling.get_predictor(pred), ns.sampling.get_corrector(corr),
-                                        lambda v: v, snr, n_steps=n_steps, probability_flow=False,
+                                        lambda v: v, snr, n_steps=n_steps, probability_flow=bool(extra.get("pf")),
                                         continuous=continuous, denoise=True, eps=eps, device="cpu")
         x, nfe = fn(model)
     finally:
@@ -302,6 +355,9 @@ def main():
     for n in SCORE_CASES:
         if a.only in (None, "score", n):
             gen_score(ns, n)
+    for n in SCORE_CASES:
+        if a.only in (None, "score64", "score64_" + n) and n != "celebahq256_ncsnpp_ve":
+            gen_score64(ns, n)
     for n in PC_CASES:
         if a.only in (None, "pc", n):
             gen_pc(ns, n)

@@ -24,7 +24,7 @@ def _fir_torch(x, k, up=1, down=1, pad=(0, 0)):
     """The same upfirdn2d written with differentiable torch ops (zero insertion, pad / crop, correlation with the
     flipped kernel, decimation: op/upfirdn2d.py:159-200) -- used only when the oracle must be differentiated."""
     B, C, H, W = x.shape
-    k = torch.as_tensor(np.asarray(k), dtype=x.dtype)
+    k = torch.as_tensor(np.asarray(k), dtype=x.dtype, device=x.device)
     kh, kw = k.shape
     y = x.reshape(B * C, 1, H, 1, W, 1)
     y = F.pad(y, [0, up - 1, 0, 0, 0, up - 1])
@@ -38,14 +38,17 @@ def _fir_torch(x, k, up=1, down=1, pad=(0, 0)):
 
 
 class RefScoreNet:
-    def __init__(self, config, state_dict, dtype=torch.float32):
+    def __init__(self, config, state_dict, dtype=torch.float32, device="cpu"):
+        """device: 'cpu' (the oracle proper) or a CUDA device -- the same torch ops then run on cuDNN / cuBLAS, which IS
+        the reference's GPU path for these layers (tests: large-batch checks; bench.py: the "kernel to beat" leg)."""
         self.cfg = config
         self.m = config.model
         self.dtype = dtype
+        self.device = torch.device(device)
         self.sd = {}
         for k, v in state_dict.items():
             k = k[len("module."):] if k.startswith("module.") else k
-            self.sd[k] = v.detach().cpu().to(dtype)
+            self.sd[k] = v.detach().to(device=self.device, dtype=dtype)
         self.nf = self.m.nf
         self.fir_k = upfirdn2d_ref.setup_kernel(self.m.fir_kernel)
 
@@ -72,7 +75,8 @@ class RefScoreNet:
 
     # -- FIR resampling (up_or_down_sampling.py:195-257, 144-178) --
     def fir(self, x, k, **kw):
-        return _fir_torch(x, k, **kw) if getattr(self, "differentiable", False) else _fir(x, k, **kw)
+        torch_form = getattr(self, "differentiable", False) or self.device.type != "cpu"
+        return _fir_torch(x, k, **kw) if torch_form else _fir(x, k, **kw)
 
     def up2(self, x):
         return self.fir(x, self.fir_k * 4, up=2, pad=(2, 1))
@@ -126,14 +130,14 @@ class RefScoreNet:
     def timestep_embedding(self, t, dim):
         half = dim // 2
         e = math.log(10000) / (half - 1)
-        e = torch.exp(torch.arange(half, dtype=torch.float32) * -e).to(self.dtype)
+        e = torch.exp(torch.arange(half, dtype=torch.float32, device=t.device) * -e).to(self.dtype)
         e = t.to(self.dtype)[:, None] * e[None, :]
         return torch.cat([torch.sin(e), torch.cos(e)], dim=1)
 
     # -- networks --
     def __call__(self, x, labels):
-        x = x.detach().cpu().to(self.dtype)
-        labels = labels.detach().cpu()
+        x = x.detach().to(device=self.device, dtype=self.dtype)
+        labels = labels.detach().to(self.device)
         with torch.no_grad():
             if self.m.name == "ddpm":
                 return self.ddpm(x, labels)

@@ -28,6 +28,7 @@ SCORE_CASES = {
                                                 "_centered": True, "_sde": "vpsde"}, 2),
     "cifar10_ncsnpp_ve": ("ve/cifar10_ncsnpp_continuous", {}, 2),
     "nc_ddpm_vp": ("vp/nc_ddpmpp", {}, 1),
+    "celebahq256_ncsnpp_ve": ("ve/celebahq_256_ncsnpp_continuous", {}, 1),
 }
 TINY = dict(nf=32, ch_mult=(1, 2), num_res_blocks=1, attn_resolutions=(8,))
 
@@ -41,6 +42,16 @@ PC_CASES = {
     "subvp_rd_none": (_POS, "subvpsde", "reverse_diffusion", "none", 0.1, 1, True, 8),
     # the full-length trajectory north_star asks for: N = 1000 PC steps (2000 network evaluations), fixed noise
     "ve_rd_langevin_1000": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 1000),
+    # the full C3 network (every conv on the tensor-core kernels), 50 PC steps = 100 forwards
+    "c3_ve_rd_langevin": ({}, "vesde", "reverse_diffusion", "langevin", 0.16, 1, True, 50,
+                          {"net": "ve/cifar10_ncsnpp_continuous"}),
+    "vp_rd_none": (dict(_POS, beta_max=5.0), "vpsde", "reverse_diffusion", "none", 0.16, 1, True, 10),
+    "ve_none_langevin": ({}, "vesde", "none", "langevin", 0.16, 1, True, 8),
+    "ve_em_none": ({}, "vesde", "euler_maruyama", "none", 0.16, 1, True, 10),
+    "subvp_em_none": (_POS, "subvpsde", "euler_maruyama", "none", 0.16, 1, True, 10),
+    "vp_rd_probflow": (dict(_POS, beta_max=5.0), "vpsde", "reverse_diffusion", "none", 0.16, 1, True, 10, {"pf": True}),
+    # (euler_maruyama + probability_flow=True raises in the reference itself: RSDE.sde returns the float 0. as
+    # diffusion and sampling.py:186 subscripts it -- no anchor for that combination)
 }
 
 
@@ -88,6 +99,11 @@ def score_case(name):
     return cfg, sd, torch.from_numpy(g["x"]), torch.from_numpy(g["labels"]), torch.from_numpy(g["out"])
 
 
+def score_fp64(name):
+    """The reference network evaluated in fp64 on the same inputs and weights (oracle/make_golden.py gen_score64)."""
+    return torch.from_numpy(np.load(os.path.join(GOLDEN, "score64_%s.npz" % name))["out64"])
+
+
 def noise_stream(seed, shape):
     gen = torch.Generator().manual_seed(int(seed))
     while True:
@@ -96,8 +112,10 @@ def noise_stream(seed, shape):
 
 def pc_case(name):
     """-> dict(cfg, sd, shape, sde_name, pred, corr, snr, n_steps, continuous, N, eps, out, nfe, noise_seed)"""
-    over, sde_name, pred, corr, snr, n_steps, continuous, N = PC_CASES[name]
-    cfg = our_config("test/tiny_ncsnpp", over)
+    tup = PC_CASES[name]
+    over, sde_name, pred, corr, snr, n_steps, continuous, N = tup[:8]
+    extra = tup[8] if len(tup) > 8 else {}
+    cfg = our_config(extra.get("net", "test/tiny_ncsnpp"), over)
     cfg.training.sde = sde_name
     cfg.training.continuous = continuous
     g = np.load(os.path.join(GOLDEN, "pc_%s.npz" % name))
@@ -105,7 +123,7 @@ def pc_case(name):
     assert abs(weight_checksum(sd) - float(g["weight_checksum"])) <= 1e-9 * float(g["weight_checksum"])
     shape = (2, cfg.data.num_channels, cfg.data.image_size, cfg.data.image_size)
     return dict(cfg=cfg, sd=sd, shape=shape, sde_name=sde_name, pred=pred, corr=corr, snr=snr, n_steps=n_steps,
-                continuous=continuous, N=N, eps=1e-5 if sde_name == "vesde" else 1e-3,
+                continuous=continuous, N=N, eps=1e-5 if sde_name == "vesde" else 1e-3, pf=bool(extra.get("pf")),
                 out=torch.from_numpy(g["out"]), nfe=int(g["nfe"]), noise_seed=int(g["noise_seed"]))
 
 

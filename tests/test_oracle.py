@@ -44,6 +44,29 @@ def test_score_oracle_matches_reference_cifar10():
     assert cases.max_rel(y, out[:1]) < 5e-5
 
 
+def test_score_oracle_matches_reference_celebahq256():
+    """Full-size C5 (256 x 256, input_skip / output_skip pyramids): one image."""
+    cfg, sd, x, labels, out = cases.score_case("celebahq256_ncsnpp_ve")
+    net = score_net_ref.RefScoreNet(cfg, sd)
+    with torch.no_grad():
+        y = net(x, labels)
+    assert cases.max_rel(y, out) < 5e-5, cases.max_rel(y, out)
+
+
+@pytest.mark.parametrize("name", ["tiny_fourier_residual", "tiny_positional_vp"])
+def test_fp64_arbiter_fixture_is_consistent(name):
+    """score64_*.npz = the reference network in fp64 on the inputs of score_*.npz: the fp32 golden sits within fp32
+    round-off of it, and the oracle restatement run in fp64 reproduces it to ~1e-12."""
+    cfg, sd, x, labels, out = cases.score_case(name)
+    out64 = cases.score_fp64(name)
+    assert out64.dtype == torch.float64 and out64.shape == out.shape
+    assert cases.rel_l2(out, out64) < 1e-5
+    net = score_net_ref.RefScoreNet(cfg, sd, dtype=torch.float64)
+    with torch.no_grad():
+        y = net(x, labels)
+    assert cases.rel_l2(y, out64) < 1e-6, cases.rel_l2(y, out64)
+
+
 @pytest.mark.parametrize("name", sorted(cases.PC_CASES))
 def test_pc_oracle_matches_reference(name):
     c = cases.pc_case(name)
@@ -53,7 +76,8 @@ def test_pc_oracle_matches_reference(name):
     sde = sampling_ref.RefSDE(c["sde_name"], c["N"], m.beta_min, m.beta_max, m.sigma_min, m.sigma_max)
     with torch.no_grad():
         x = sampling_ref.pc_sample(sde, net, c["shape"], c["pred"], c["corr"], c["snr"], c["n_steps"], c["continuous"],
-                                   cases.noise_stream(c["noise_seed"], c["shape"]), denoise=True, eps=c["eps"])
+                                   cases.noise_stream(c["noise_seed"], c["shape"]), denoise=True, eps=c["eps"],
+                                   probability_flow=c["pf"])
     assert c["nfe"] == c["N"] * (c["n_steps"] + 1)
     assert cases.rel_l2(x, c["out"]) < 1e-4, cases.rel_l2(x, c["out"])
 
