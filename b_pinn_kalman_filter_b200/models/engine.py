@@ -507,6 +507,7 @@ class ScoreEngine:
                         # forward_for_grad and input_grad (a `model(x, t)` call, a PC step): private buffers, not the
                         # engine-wide free list that every other plan is packed into
                         b.ws = Workspace(self.device)
+                        b.plan.keep.append(b.ws)       # the plan owns it: its launch arguments are raw pointers into it
                     self.net_builder(b, self.config)
                     b.plan.n_fwd = len(b.plan.ops)
                     if grad:
