@@ -53,6 +53,9 @@ struct ConvTcParams {
   // OUTPUT values, [B][slots][Cout][2] fp32; slots = 2 * tiles per image when a tile lies inside one image, else 1
   float* stats;
   int stat_slots;
+  // GNF variants: the A operand is GroupNorm + SiLU of the raw source(s), applied in shared memory between the TMA load
+  // and the MMA.  [B][C1 + C2][2] fp32 = (scale / 2, shift / 2) per (image, channel) from b200_gn_coef.
+  const float* gn_coef;
 };
 
 // DS (1x1 convolutions: a handful of K blocks per tile, so the kernel is bound by its epilogue, not by the operand
@@ -145,13 +148,23 @@ template <int BN, bool DS> struct TcSmemSel<BN, false, DS, true> { using type = 
 template <int BN, bool DS> struct TcSmemSel<BN, true, DS, true> { using type = TcSmemHaloPairT<DS, BN>; };
 using TcSmemHaloPair = TcSmemHaloPairT<false>;
 
-template <int BN, int EPI, bool HALO = false, bool DS = false, bool PAIR = false>
-__global__ void __launch_bounds__(TC_THREADS + (HALO ? 32 : 0), 1)
+// GNF (halo + pair variants only): GroupNorm + SiLU of the INPUT fused into the operand pipeline.  The conv consumes
+// the producer's raw output; four extra warps rewrite every landed activation stage in place,
+//     h = fma(x, scale/2, shift/2);  y = fma(h, tanh.approx(h), h)          (= silu(x * scale + shift), bit for bit what
+// gn_apply_kernel<bf16> writes), and only then is the stage handed to the MMA issuer.  The standalone GroupNorm pass
+// (one read + one write of every activation, ~23 % of the C3 forward) disappears.  The three column-shifted boxes of a
+// stage overlap: each of the 10 x 18 unique pixels is transformed ONCE by its owner thread, which reads the raw value
+// from the one box copy nobody else reads and stores the result into every box that holds that pixel (<= 3 stores).
+// Zero padding stays zero: out-of-image pixels (TMA zero fill) are skipped.
+constexpr int TC_XF_WARPS = 4;
+template <int BN, int EPI, bool HALO = false, bool DS = false, bool PAIR = false, bool GNF = false>
+__global__ void __launch_bounds__(TC_THREADS + (HALO ? 32 : 0) + (GNF ? 32 * TC_XF_WARPS : 0), 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapOut,
                const __grid_constant__ CUtensorMap mapRes, const ConvTcParams p) {
   using S = typename TcSmemSel<BN, HALO, DS, PAIR>::type;
   static_assert(!PAIR || (EPI == 0 && ((BN == 256 && !DS) || (BN == 128 && HALO))), "pair variants");
+  static_assert(!GNF || (HALO && PAIR), "GroupNorm-fused operand pipeline: halo + pair variants only");
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;   // 0 = leader (issues the MMAs)
   constexpr int NWS = HALO ? (PAIR ? TcSmemHaloPairT<DS, BN>::WSTAGES : TcSmem<BN, true>::WSTAGES) : 0;   // weight ring (halo)
   extern __shared__ uint8_t smem_raw[];
@@ -166,6 +179,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   auto wempty_bar = [&](int s) { return bar0 + 8u * (2 * S::STAGES + 4 + NWS + s); };
   const uint32_t res_bar = bar0 + 8u * (2 * S::STAGES + 4 + 2 * NWS);      // residual tile landed in the staging buffer
   const uint32_t tmem_slot = res_bar + 8u;
+  auto xf_bar = [&](int s) { return res_bar + 16u + 8u * s; };             // GNF: stage transformed (leader's copy counts)
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   // the warp index through a shuffle: provably warp-uniform, so the role branches below are convergent for ptxas
@@ -185,6 +199,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
     for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), PAIR ? 16 : 8); }   // PAIR: both CTAs' epilogue warps
     for (int w = 0; w < NWS; ++w) { mbar_init(wfull_bar(w), 1); mbar_init(wempty_bar(w), 1); }
     mbar_init(res_bar, 1);
+    if constexpr (GNF) for (int s = 0; s < S::STAGES; ++s) mbar_init(xf_bar(s), 2 * TC_XF_WARPS);   // both CTAs' warps
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA1) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapW) : "memory");
@@ -234,7 +249,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             if (elected) {
             const uint32_t sa = base + stage * S::A_BYTES;
             const int c = kb * TC_BK;
-            if constexpr (PAIR) {
+            // (GNF: each CTA's boxes complete on its OWN barrier -- its own transform warps consume them first)
+            if constexpr (PAIR && !GNF) {
               const uint32_t lbar = mapa_cta(full_bar(stage), 0);
               if (cta_rank == 0) mbar_expect_tx(full_bar(stage), 2 * S::A_BYTES);
 #pragma unroll
@@ -335,7 +351,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
         const uint32_t d_tmem = tmem_u + (uint32_t)(acc * BN);
         if constexpr (HALO) {
           for (int kb = 0; kb < kb_per_tap; ++kb) {
-            mbar_wait(full_bar(stage), phase);
+            if constexpr (GNF) mbar_wait_cluster(xf_bar(stage), phase); else mbar_wait(full_bar(stage), phase);
             tc_fence_after();
             const uint32_t sa = base + stage * S::A_BYTES;
             const uint64_t da0 = make_sw128_desc(sa);
@@ -644,6 +660,61 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+  } else if (GNF && warp >= 11) {
+    // ================= GroupNorm + SiLU transform warps (11..14) =================
+    if constexpr (GNF) {
+      const int tt = (int)threadIdx.x - 11 * 32;                   // 0 .. 127
+      const int u = tt & 7;                                        // 16-byte unit of a pixel row = 8 channels
+      uint8_t* const sgen = smem_raw + (base - smem_u32(smem_raw));
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = tile_first; tile < tile_end; tile += tile_step) {
+        int mt, nt, b0, h0, w0;
+        tile_coords(tile, mt, nt);
+        m_origin(mt, b0, h0, w0);
+        const bool live = b0 < p.B;                                // (odd tail tile of a pair: nothing but zero fill)
+        for (int kb = 0; kb < kb_per_tap; ++kb) {
+          float4 cf[4];                                            // (scale/2, shift/2) of this thread's 8 channels
+          if (live) {
+            const float4* cp = reinterpret_cast<const float4*>(p.gn_coef + ((size_t)b0 * Ctot + kb * TC_BK + u * 8) * 2);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) cf[i] = __ldg(cp + i);
+          }
+          mbar_wait(full_bar(stage), phase);                       // this CTA's three boxes have landed
+          if (live) {
+            uint8_t* const sa = sgen + stage * S::A_BYTES;
+#pragma unroll 4
+            for (int q = tt >> 3; q < 10 * (HALO_TH + 2); q += 4 * TC_XF_WARPS) {
+              const int r = q / 10, j = q - r * 10;                // unique pixel: row r of the boxes, column w0 - 1 + j
+              if ((unsigned)(h0 - 1 + r) < (unsigned)p.H && (unsigned)(w0 - 1 + j) < (unsigned)p.W) {
+                const int sbox = j == 0 ? 0 : (j == 9 ? 2 : 1), scol = j - sbox;
+                uint8_t* const row = sa + r * (HALO_TW * 128);
+                const uint4 v = *reinterpret_cast<const uint4*>(row + sbox * S::BOX_BYTES + scol * 128 + ((u ^ scol) << 4));
+                const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+                uint32_t o4[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float h0f = fmaf(__uint_as_float(w4[i] << 16), cf[i].x, cf[i].y);
+                  const float h1f = fmaf(__uint_as_float(w4[i] & 0xffff0000u), cf[i].z, cf[i].w);
+                  float t0, t1;
+                  asm("tanh.approx.f32 %0, %1;" : "=f"(t0) : "f"(h0f));
+                  asm("tanh.approx.f32 %0, %1;" : "=f"(t1) : "f"(h1f));
+                  const __nv_bfloat162 pk = __floats2bfloat162_rn(fmaf(h0f, t0, h0f), fmaf(h1f, t1, h1f));
+                  o4[i] = *reinterpret_cast<const uint32_t*>(&pk);
+                }
+                const uint4 o = make_uint4(o4[0], o4[1], o4[2], o4[3]);
+                if (j <= 7) *reinterpret_cast<uint4*>(row + j * 128 + ((u ^ j) << 4)) = o;
+                if (j >= 1 && j <= 8) *reinterpret_cast<uint4*>(row + S::BOX_BYTES + (j - 1) * 128 + ((u ^ (j - 1)) << 4)) = o;
+                if (j >= 2) *reinterpret_cast<uint4*>(row + 2 * S::BOX_BYTES + (j - 2) * 128 + ((u ^ (j - 2)) << 4)) = o;
+              }
+            }
+          }
+          fence_proxy_async_smem();                                // generic-proxy writes -> visible to the MMA's reads
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_cta(xf_bar(stage), 0));
+          if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
   }
   if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tc_fence_before();
@@ -753,12 +824,12 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
   B200_RETURN_LAST();
 }
 
-template <int BN, bool HALO, bool DS = false>
+template <int BN, bool HALO, bool DS = false, bool GNF = false>
 int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
                 const ConvTcParams& p, cudaStream_t st) {
   using SP = typename TcSmemSel<BN, HALO, DS, true>::type;
   static int attr_state[B200_MAX_DEVICES];
-  auto kern = conv_tc_kernel<BN, 0, HALO, DS, true>;
+  auto kern = conv_tc_kernel<BN, 0, HALO, DS, true, GNF>;
   if (int rc = b200_set_smem_once(attr_state, kern, SP::TOTAL)) return rc;
   CUtensorMap rm = om;
   if (p.res) {
@@ -768,7 +839,8 @@ int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap&
   const int pairs = ((p.num_m + 1) / 2) * p.num_n;
   const int clusters = pairs < B200_NUM_SMS / 2 ? pairs : B200_NUM_SMS / 2;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(TC_THREADS + (HALO ? 32 : 0)); cfg.dynamicSmemBytes = SP::TOTAL;
+  cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(TC_THREADS + (HALO ? 32 : 0) + (GNF ? 32 * TC_XF_WARPS : 0));
+  cfg.dynamicSmemBytes = SP::TOTAL;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -852,10 +924,60 @@ extern "C" int b200_conv2d_tc_supported(int C1, int C2, int B, int H, int W, int
   return 1;
 }
 
+// Which tile variant a stride-1 convolution of this shape runs as (shared by the launcher and by
+// b200_conv2d_tc_gn_supported): BN, and whether it is one of the halo + pair variants.
+static void conv_tc_variant(int B, int H, int W, int Cout, int ksize, int out_mode, int& BN, bool& halo_pair) {
+  int TW, TH, TB, tw, th;
+  tile_box(B, H, W, TW, TH, TB, tw, th);
+  const int num_m = TB > 1 ? (B + TB - 1) / TB : B * tw * th;
+  BN = out_mode != 0 ? 16 : ((Cout % 256 == 0) ? 256 : 128);
+  static const int pair_min = [] { const char* e = getenv("B200_CONV_PAIR_MIN"); return e ? atoi(e) : 48; }();
+  const bool pair_small = out_mode == 0 && ksize == 3 && pair_enabled() && ((num_m + 1) / 2) * (Cout / 256) >= pair_min;
+  if (BN == 256 && num_m * (Cout / 256) < B200_NUM_SMS && !pair_small) BN = 128;
+  static const bool hp256 = [] { const char* e = getenv("B200_CONV_HALO_PAIR256"); return !(e && e[0] == '0'); }();
+  const bool halo256 = BN == 256 && hp256 && halo_pair_enabled() && pair_enabled();
+  halo_pair = out_mode == 0 && (BN == 128 || halo256) && ksize == 3 && TB == 1 && H % HALO_TH == 0 && W % HALO_TW == 0 &&
+              halo_enabled() && halo_pair_enabled();
+}
+
+// 1: a 3x3 convolution of this shape can take its input through the GroupNorm-fused operand pipeline (b200_conv2d_tc_gn)
+extern "C" int b200_conv2d_tc_gn_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize) {
+  if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1, 0)) return 0;
+  static const bool on = [] { const char* e = getenv("B200_CONV_GN_FUSE"); return !(e && e[0] == '0'); }();
+  int BN; bool hp;
+  conv_tc_variant(B, H, W, Cout, ksize, 0, BN, hp);
+  return (on && hp) ? 1 : 0;
+}
+
+static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
+                          const float* temb, int temb_stride, const void* res, float out_scale, void* out,
+                          int out_mode, const float* sample_mul, float* stats, const float* gn_coef, int B, int H, int W,
+                          int Cout, int ksize, cudaStream_t st);
+
 extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
                               const float* temb, int temb_stride, const void* res, float out_scale, void* out,
                               int out_mode, const float* sample_mul, float* stats, int B, int H, int W, int Cout,
                               int ksize, cudaStream_t st) {
+  return conv2d_tc_impl(x1, C1, x2, C2, w, bias, temb, temb_stride, res, out_scale, out, out_mode, sample_mul, stats,
+                        nullptr, B, H, W, Cout, ksize, st);
+}
+
+// conv(silu(groupnorm(cat(x1, x2)))) with the normalisation applied inside the operand pipeline: x1 / x2 are the RAW
+// producer outputs and gn_coef = [B][C1 + C2][2] (scale / 2, shift / 2) from b200_gn_coef.  Replaces
+// `h = act(GroupNorm(x)); h = Conv(h)` of the residual blocks (models/layerspp.py:242-246, 264-266) without writing h.
+extern "C" int b200_conv2d_tc_gn(const void* x1, int C1, const void* x2, int C2, const float* gn_coef, const void* w,
+                                 const float* bias, const float* temb, int temb_stride, const void* res, float out_scale,
+                                 void* out, float* stats, int B, int H, int W, int Cout, int ksize, cudaStream_t st) {
+  if (!gn_coef) return B200_ERR_ARG;
+  if (!b200_conv2d_tc_gn_supported(C1, C2, B, H, W, Cout, ksize)) return B200_ERR_UNSUPPORTED;
+  return conv2d_tc_impl(x1, C1, x2, C2, w, bias, temb, temb_stride, res, out_scale, out, 0, nullptr, stats, gn_coef, B, H,
+                        W, Cout, ksize, st);
+}
+
+static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
+                          const float* temb, int temb_stride, const void* res, float out_scale, void* out,
+                          int out_mode, const float* sample_mul, float* stats, const float* gn_coef, int B, int H, int W,
+                          int Cout, int ksize, cudaStream_t st) {
   if (!x1 || !w || !out || (C2 > 0 && !x2)) return B200_ERR_ARG;
   if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1, out_mode)) return B200_ERR_UNSUPPORTED;
   if ((out_mode == 1 && (temb || res)) || (out_mode == 2 && temb)) return B200_ERR_UNSUPPORTED;
@@ -875,6 +997,7 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
   p.bias = bias; p.temb = temb; p.temb_stride = temb_stride; p.res = (const bf16*)res; p.out_scale = out_scale;
   p.out = (bf16*)out; p.out_nchw = (float*)out; p.sample_mul = sample_mul; p.cout_true = Cout;
   p.stats = out_mode == 0 ? stats : nullptr; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h;
+  p.gn_coef = gn_coef;
   const int Ktot = ksize * ksize * (C1 + C2);
   CUtensorMap a1, a2, wm;
   int rc = act_map(&a1, x1, B, H, W, C1, p.TW, p.TH, p.TB);
@@ -902,6 +1025,7 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
       CUtensorMap wh;                                     // each CTA of the pair loads 128 of the 256 weight rows
       rc = weight_map(&wh, w, Cout, Ktot, 128);
       if (rc) return rc;
+      if (gn_coef) return launch_pair<256, true, false, true>(a1, a2, wh, om, p, st);
       return launch_pair<256, true>(a1, a2, wh, om, p, st);
     }
     if (halo_pair_enabled()) {
@@ -911,11 +1035,14 @@ extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, co
       // B200_CONV_HALO_PAIR_DS=1: second staging buffer instead of the third weight-ring stage for convs with a
       // residual (measured: 128->128 0.304 -> 0.299 ms, 256->128 0.505 -> 0.529 ms; off)
       static const bool hp_ds = [] { const char* e = getenv("B200_CONV_HALO_PAIR_DS"); return e && e[0] == '1'; }();
+      if (gn_coef) return launch_pair<128, true, false, true>(a1, a2, wh, om, p, st);
       if (res && hp_ds) return launch_pair<128, true, true>(a1, a2, wh, om, p, st);
       return launch_pair<128, true>(a1, a2, wh, om, p, st);
     }
+    if (gn_coef) return B200_ERR_UNSUPPORTED;
     return launch<128, 0, true>(a1, a2, wm, om, p, st);
   }
+  if (gn_coef) return B200_ERR_UNSUPPORTED;
   rc = act_map(&om, out, B, H, W, Cout, p.TW, p.TH, p.TB);
   if (rc) return rc;
   if (ksize == 3 && BN == 256 && pair_enabled()) {
@@ -953,7 +1080,7 @@ extern "C" int b200_conv2d_tc_s2(const void* x, int C, const void* w, const floa
   p.num_n = Cout / BN;
   p.bias = bias; p.temb = nullptr; p.temb_stride = 0; p.res = (const bf16*)res; p.out_scale = out_scale;
   p.out = (bf16*)out; p.out_nchw = nullptr; p.sample_mul = nullptr; p.cout_true = Cout; p.narrow = 0;
-  p.stats = stats; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h;
+  p.stats = stats; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h; p.gn_coef = nullptr;
   CUtensorMap a1, wm, om;
   int rc = act_map(&a1, x, B, Hin, Win, C, p.TW, p.TH, p.TB, 2);
   if (rc) return rc;

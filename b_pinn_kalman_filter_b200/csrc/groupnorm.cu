@@ -170,6 +170,50 @@ __global__ void __launch_bounds__(256) gn_apply_kernel(GnArgs a) {
   }
 }
 
+// GroupNorm coefficients for the GroupNorm-fused convolution (b200_conv2d_tc_gn): the same statistics fold as
+// gn_apply_kernel<bf16> (fp32, slots then channels in a fixed order: identical mean / rstd), written per (image,
+// channel) as (scale / 2, shift / 2) so that the consumer evaluates silu(x scale + shift) = h + h tanh(h) with
+// h = fma(x, scale / 2, shift / 2) -- halving is exact, so the fused path reproduces gn_apply's output bit for bit.
+__global__ void __launch_bounds__(256) gn_coef_kernel(GnArgs a, float* __restrict__ coef) {
+  extern __shared__ float sh[];  // [G] mean, [G] rstd, [C] sums, [C] sums of squares
+  const int C = a.C1 + a.C2, cpg = C / a.G;
+  const int b = blockIdx.x;
+  float* chs = sh + 2 * a.G;
+  b200_pdl_wait();
+  b200_pdl_trigger();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const bool first = c < a.C1;
+    const float* base = first ? a.st1 + ((size_t)b * a.T1 * a.C1 + c) * 2
+                              : a.st2 + ((size_t)b * a.T2 * a.C2 + (c - a.C1)) * 2;
+    const int nslot = first ? a.T1 : a.T2, cs = first ? a.C1 : a.C2;
+    float ts = 0, tq = 0;
+    for (int k = 0; k < nslot; ++k) {
+      const float2 v = __ldg(reinterpret_cast<const float2*>(base + (size_t)k * cs * 2));
+      ts += v.x; tq += v.y;
+    }
+    chs[c] = ts; chs[C + c] = tq;
+  }
+  __syncthreads();
+  for (int g = threadIdx.x; g < a.G; g += blockDim.x) {
+    float ts = 0, tq = 0;
+    for (int c = g * cpg; c < (g + 1) * cpg; ++c) { ts += chs[c]; tq += chs[C + c]; }
+    const float rn = 1.0f / ((float)a.HW * (float)cpg);
+    const float mean = ts * rn;
+    float var = tq * rn - mean * mean;
+    if (var < 0.0f) var = 0.0f;
+    sh[g] = mean;
+    sh[a.G + g] = gn_rsqrt(var + a.eps);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int g = c / cpg;
+    const float ga = a.gamma ? a.gamma[c] : 1.0f, be = a.beta ? a.beta[c] : 0.0f;
+    const float sc = sh[a.G + g] * ga;
+    const float sf = be - sh[g] * sc;
+    reinterpret_cast<float2*>(coef)[(size_t)b * C + c] = make_float2(0.5f * sc, 0.5f * sf);
+  }
+}
+
 static int gn_threads(int C) {
   const int CV = C / 8;
   if (CV <= 0 || CV > 256) return 0;
@@ -255,6 +299,26 @@ extern "C" int b200_gn_apply_stats(const void* x1, int C1, const float* st1, int
   if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float>, dim3(B * nsplit), dim3(thr), smem, st, a);
   else if (dtype == B200_DT_BF16) le = b200_launch_pdl(gn_apply_kernel<bf16>, dim3(B * nsplit), dim3(thr), smem, st, a);
   else return B200_ERR_ARG;
+  if (le != cudaSuccess) return -(1000 + (int)le);
+  B200_RETURN_LAST();
+}
+
+// (scale / 2, shift / 2) per (image, channel) of GroupNorm over cat(x1, x2) from the producers' statistics by-products:
+// coef = [B][C1 + C2][2] fp32, consumed by b200_conv2d_tc_gn (which applies GroupNorm + SiLU inside its operand
+// pipeline).  bf16 activations only (the statistics are those of bf16 outputs).
+extern "C" int b200_gn_coef(const float* st1, int T1, int C1, const float* st2, int T2, int C2, int B, int HW, int G,
+                            const float* gamma, const float* beta, float eps, float* coef, cudaStream_t st) {
+  const int C = C1 + C2;
+  if (!st1 || !coef || T1 <= 0 || C1 <= 0 || C2 < 0 || (C2 > 0 && (!st2 || T2 <= 0)) || B < 0 || HW <= 0 || G <= 0)
+    return B200_ERR_ARG;
+  if (C1 % 8 || C2 % 8 || C % G) return B200_ERR_UNSUPPORTED;
+  if (B == 0) return B200_OK;
+  GnArgs a;
+  a.x1 = nullptr; a.x2 = nullptr; a.C1 = C1; a.C2 = C2; a.B = B; a.HW = HW; a.G = G; a.nsplit = 1; a.partial = nullptr;
+  a.gamma = gamma; a.beta = beta; a.eps = eps; a.act = 1; a.out = nullptr;
+  a.st1 = st1; a.st2 = st2; a.T1 = T1; a.T2 = T2;
+  const size_t smem = (size_t)(2 * G + 2 * C) * sizeof(float);
+  cudaError_t le = b200_launch_pdl(gn_coef_kernel, dim3(B), dim3(256), smem, st, a, coef);
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
 }

@@ -14,6 +14,7 @@ Design:
 """
 import ctypes
 import math
+import os
 
 import torch
 
@@ -56,6 +57,18 @@ class Act:
     def at(self, byte_offset):
         """Pointer argument `byte_offset` bytes into this activation (resolved when the plan is finalised)."""
         return Ptr(self, byte_offset)
+
+
+class LazyGN(Act):
+    """GroupNorm + SiLU whose launch is deferred to its first consumer: a tensor-core 3x3 convolution that supports the
+    GroupNorm-fused operand pipeline takes the RAW sources plus a coefficient table (no normalised tensor is ever
+    written); any other consumer makes `Builder.emit` materialise it with b200_gn_apply_stats first."""
+    __slots__ = ("src1", "src2", "key", "groups", "real")
+
+    def __init__(self, src1, src2, key, groups):
+        C = src1.C + (src2.C if src2 is not None else 0)
+        super().__init__(None, src1.B, src1.H, src1.W, C)
+        self.src1, self.src2, self.key, self.groups, self.real = src1, src2, key, groups, None
 
 
 class Ptr:
@@ -209,7 +222,27 @@ class Builder:
         self.plan.keep.append(t)
         return t
 
+    def materialize(self, gn):
+        """The normalised tensor of a deferred GroupNorm (emits its b200_gn_apply_stats launch on first use)."""
+        if gn.real is None:
+            from . import tc
+            x, x2 = gn.src1, gn.src2
+            out = self.new(x.H, x.W, gn.C)
+            s1, t1 = tc.request_stats(self, x)
+            s2, t2 = tc.request_stats(self, x2) if x2 is not None else (None, 0)
+            p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+            HW = x.H * x.W
+            gn.real = out
+            self.emit("b200_gn_apply_stats", x, x.C, s1, t1, p2, c2, s2, t2, self.dt, self.B, HW, gn.groups,
+                      self.lib.b200_gn_nsplit(self.B, HW), self.e.dev(gn.key + ".weight"), self.e.dev(gn.key + ".bias"),
+                      1e-6, 1, out)
+        return gn.real
+
     def emit(self, name, *args, flops=0, tag=""):
+        if any(isinstance(a, LazyGN) or (isinstance(a, Ptr) and isinstance(a.act, LazyGN)) for a in args):
+            args = tuple(self.materialize(a) if isinstance(a, LazyGN) else
+                         (Ptr(self.materialize(a.act), a.off) if isinstance(a, Ptr) and isinstance(a.act, LazyGN) else a)
+                         for a in args)
         fn = getattr(self.lib, name)
         self.plan.ops.append((fn, args, name))
         self.plan.meta.append((name, int(flops)))
@@ -229,6 +262,8 @@ class Builder:
         p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
         if self.e.use_tc and self.e.fuse_gn_stats and x.producer is not None and (x2 is None or x2.producer is not None):
             from . import tc
+            if act and self.tape is None and self.e.fuse_gn_conv and tc.FUSE_GN:
+                return LazyGN(x, x2, key, groups)          # resolved by its first consumer (see LazyGN)
             s1, t1 = tc.request_stats(self, x)
             s2, t2 = tc.request_stats(self, x2) if x2 is not None else (None, 0)
             self.emit("b200_gn_apply_stats", x, x.C, s1, t1, p2, c2, s2, t2, self.dt, self.B, HW, groups, ns,
@@ -349,6 +384,9 @@ class ScoreEngine:
         self.dt = {"bf16": DT_BF16, "fp32": DT_F32}[precision]
         self.use_tc = bool(use_tensor_cores) and self.dt == DT_BF16
         self.fuse_gn_stats = True           # GroupNorm statistics as a by-product of the producing conv's epilogue
+        # GroupNorm + SiLU applied inside the consuming conv's operand pipeline (B200_FUSE_GN=0: A/B measurements)
+        self.fuse_gn_conv = os.environ.get("B200_FUSE_GN", "1") != "0"
+        self.gn_fused = 0
         self.workspace = Workspace(self.device)
         self.params = {}           # reference-layout fp32 tensors on device
         self._packed = {}
@@ -453,6 +491,12 @@ class ScoreEngine:
     # ---- kernel selection -------------------------------------------------------------------------------------
     def emit_conv(self, b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, stride, pad, key):
         from . import tc
+        if (isinstance(x, LazyGN) and x.real is None and x2 is None and self.use_tc
+                and tc.conv_gn_supported(b, x.src1, x.src2, out, ksize, stride, tuple(pad))):
+            tc.emit_conv_gn(b, x, w, bias, temb_ptr, res, out_scale, out, ksize, self.conv_flops(b, x, x2, out, ksize))
+            self.tc_convs += 1
+            self.gn_fused += 1
+            return
         if (self.use_tc and stride == 2 and ksize == 3 and tuple(pad) == (0, 0) and x2 is None and temb_ptr is None
                 and tc.s2_supported(b, x, out)):
             tc.emit_s2(b, x, w, bias, res, out_scale, out, self.conv_flops(b, x, x2, out, ksize))

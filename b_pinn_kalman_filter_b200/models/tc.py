@@ -15,7 +15,14 @@ _lib.register_signature("b200_conv2d_tc_stat_slots", [c_int] * 3)
 _lib.register_signature("b200_gn_apply_stats", [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int,
                                                 c_int, c_int, c_vp, c_vp, c_float, c_int, c_vp, c_vp])
 
+_lib.register_signature("b200_gn_coef", [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_float,
+                                        c_vp])
+_lib.register_signature("b200_conv2d_tc_gn_supported", [c_int] * 7)
+_lib.register_signature("b200_conv2d_tc_gn", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float,
+                                              c_vp, c_vp, c_int, c_int, c_int, c_int, c_int])
+
 ENABLED = True
+FUSE_GN = True        # GroupNorm + SiLU inside the consumer conv's operand pipeline (b200_conv2d_tc_gn)
 
 
 def conv_supported(b, x, x2, out, ksize, stride, pad):
@@ -31,6 +38,29 @@ def emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
            out, 0, None, None, b.B, x.H, x.W, out.C, ksize, flops=flops,
            tag="%dx%d %dx%d %d->%d" % (ksize, ksize, x.H, x.W, x.C + c2, out.C))
     out.producer = (len(b.plan.ops) - 1, 13)      # (launch index, position of the `stats` argument)
+
+
+def conv_gn_supported(b, x1, x2, out, ksize, stride, pad):
+    """Can `conv(silu(groupnorm(cat(x1, x2))))` run with the normalisation inside the conv (raw sources x1 / x2)?"""
+    if not (ENABLED and FUSE_GN) or ksize != 3 or stride != 1 or pad != (1, 1) or (out.H, out.W) != (x1.H, x1.W):
+        return False
+    c2 = x2.C if x2 is not None else 0
+    return bool(_lib.lib().b200_conv2d_tc_gn_supported(x1.C, c2, b.B, x1.H, x1.W, out.C, ksize))
+
+
+def emit_conv_gn(b, gn, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
+    """`gn`: a deferred GroupNorm (engine.LazyGN).  Emits the coefficient fold + the GroupNorm-fused convolution."""
+    x1, x2 = gn.src1, gn.src2
+    s1, t1 = request_stats(b, x1)
+    s2, t2 = request_stats(b, x2) if x2 is not None else (None, 0)
+    p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+    coef = b.f32(b.B * (x1.C + c2) * 2)
+    b.emit("b200_gn_coef", s1, t1, x1.C, s2, t2, c2, b.B, x1.H * x1.W, gn.groups, b.e.dev(gn.key + ".weight"),
+           b.e.dev(gn.key + ".bias"), 1e-6, coef.data_ptr())
+    b.emit("b200_conv2d_tc_gn", x1, x1.C, p2, c2, coef.data_ptr(), w.data_ptr(), bias.data_ptr(), temb_ptr,
+           b.temb_stride, res, out_scale, out, None, b.B, x1.H, x1.W, out.C, ksize, flops=flops,
+           tag="%dx%d %dx%d %d->%d gn" % (ksize, ksize, x1.H, x1.W, x1.C + c2, out.C))
+    out.producer = (len(b.plan.ops) - 1, 12)      # position of the `stats` argument
 
 
 def head_supported(b, x, cout, ksize):

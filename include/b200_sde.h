@@ -130,6 +130,19 @@ int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w
  * squares of the bf16 output, [B][slots][Cout][2] fp32 with slots = b200_conv2d_tc_stat_slots(B, H, W); consumed by
  * b200_gn_apply_stats, so the separate statistics pass over the activation disappears. */
 int b200_conv2d_tc_stat_slots(int B, int H, int W);
+/* GroupNorm + SiLU of the INPUT fused into the convolution's operand pipeline: `h = act(GroupNorm(x)); h = Conv(h)` of
+ * the residual blocks (models/layerspp.py:242-246, 264-266; models/layers.py:640-647) without ever writing h.
+ * b200_gn_coef folds the producers' `stats` by-products into coef = [B][C1+C2][2] fp32 (scale/2, shift/2) per (image,
+ * channel) of GroupNorm(G groups, eps) over cat(x1, x2); b200_conv2d_tc_gn then convolves the RAW x1 / x2: extra warps
+ * rewrite each TMA-landed activation stage in shared memory (h = fma(x, scale/2, shift/2); h + h tanh(h)) before the
+ * MMA reads it; zero padding stays zero.  Bit-identical to b200_gn_apply_stats followed by b200_conv2d_tc.  Taken for
+ * the 3x3 shapes b200_conv2d_tc_gn_supported accepts (the halo + CTA-pair tile variants: H % 16 == 0, W % 8 == 0). */
+int b200_gn_coef(const float* st1, int T1, int C1, const float* st2, int T2, int C2, int B, int HW, int G,
+                 const float* gamma, const float* beta, float eps, float* coef, cudaStream_t stream);
+int b200_conv2d_tc_gn_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize);
+int b200_conv2d_tc_gn(const void* x1, int C1, const void* x2, int C2, const float* gn_coef, const void* w,
+                      const float* bias, const float* temb, int temb_stride, const void* res, float out_scale, void* out,
+                      float* stats, int B, int H, int W, int Cout, int ksize, cudaStream_t stream);
 /* 3x3 stride-2 VALID conv (zero beyond the input extent) on the same tensor-core kernel (TMA element strides):
  * F.conv2d(stride=2) of conv_downsample_2d (models/up_or_down_sampling.py:174-178) on the FIR-padded input, and
  * DDPM's pad(0,1,0,1)+conv3x3/2 (models/layers.py:596-608).  x [B,Hin,Win,C] bf16, out [B,Ho,Wo,Cout] bf16. */
