@@ -34,6 +34,8 @@ _SIGNATURES = {
                       c_vp],
     "b200_sample_sumsq": [c_vp, c_vp, c_vp, c_vp, c_int, c_ll, c_u64, c_u64, c_ll, c_vp, c_vp],
     "b200_langevin_norm_sums": [c_vp, c_vp, c_vp, c_int, c_vp],
+    "b200_langevin_norms_static_max_batch": [],
+    "b200_langevin_norms_static": [c_vp, c_vp, c_vp, c_int, c_ll, c_u64, c_u64, c_ll, c_vp, c_vp],
     "b200_sde_update": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_float, c_int, c_ll,
                         c_u64, c_u64, c_ll, c_vp],
     "b200_fill_normal": [c_vp, c_ll, c_float, c_u64, c_u64, c_ll, c_vp],
@@ -77,7 +79,8 @@ def lib():
     return _lib
 
 
-_ERR = {-1: "bad argument", -2: "unsupported shape", -3: "CUDA driver entry point unavailable"}
+_ERR = {-1: "bad argument", -2: "unsupported shape", -3: "CUDA driver entry point unavailable",
+        -4: "size beyond the static scratch capacity of an allocation-free entry point"}
 
 
 def check(rc, what):

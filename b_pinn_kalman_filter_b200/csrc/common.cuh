@@ -10,6 +10,7 @@
 #define B200_ERR_ARG (-1)
 #define B200_ERR_UNSUPPORTED (-2)
 #define B200_ERR_DRIVER (-3)
+#define B200_ERR_TOO_LARGE (-4)   /* size beyond the capacity of a static-scratch entry point */
 
 // Every launcher returns B200_OK or -(1000 + cudaError) so the host side can raise.
 #define B200_RETURN_LAST()                                        \

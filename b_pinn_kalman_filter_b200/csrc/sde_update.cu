@@ -205,3 +205,60 @@ extern "C" int b200_step_advance(int* step, int delta, cudaStream_t st) {
   step_advance_kernel<<<1, 32, 0, st>>>(step, delta);
   B200_RETURN_LAST();
 }
+
+// ---- allocation-free Langevin norms ---------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  The two-launch reduction above needs
+// a caller-provided [2][B] fp32 scratch (per-sample sums of squares of the score and of the noise); here that scratch
+// is a file-scope device array, so the call allocates NOTHING (no cudaMalloc / cudaFree / allocating library routine).
+//   * capacity: B <= B200_NORMS_STATIC_MAX_B (16384) samples; the array is 128 KB and every GPU that loads the library
+//     holds it until the process exits;
+//   * every call shares the one array and it keeps the previous call's contents: nothing has to start at zero -- each
+//     call writes entries [0, B) of both halves before it reads them -- but two calls that overlap on the GPU (different
+//     streams, or different host threads without ordering) RACE on it.  Calls on one stream are ordered and safe.
+// In host code `g_norms_scratch` is only a host-side stand-in for the symbol: its device address is looked up once per
+// device with cudaGetSymbolAddress (that device current) and that pointer is what the kernels receive.
+#define B200_NORMS_STATIC_MAX_B 16384
+static __device__ __align__(256) float g_norms_scratch[2 * B200_NORMS_STATIC_MAX_B];
+
+namespace {
+float* g_norms_ptr[B200_MAX_DEVICES];      // device address of g_norms_scratch on each device (nullptr: not looked up)
+cudaError_t g_norms_err[B200_MAX_DEVICES];
+
+int norms_scratch_ptr(float** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return -(1000 + (int)e);
+  if (dev < 0 || dev >= B200_MAX_DEVICES) return B200_ERR_ARG;
+  if (!g_norms_ptr[dev]) {
+    // racing host threads look the same address up twice: idempotent
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_norms_scratch);
+    if (e != cudaSuccess || !p) { g_norms_err[dev] = e; return -(1000 + (int)(e == cudaSuccess ? cudaErrorInvalidSymbol : e)); }
+    g_norms_ptr[dev] = static_cast<float*>(p);
+  }
+  *out = g_norms_ptr[dev];
+  return B200_OK;
+}
+}  // namespace
+
+extern "C" int b200_langevin_norms_static_max_batch(void) { return B200_NORMS_STATIC_MAX_B; }
+
+// sums2[0] = sum_b ||score_b||_2, sums2[1] = sum_b ||z_b||_2 (z == NULL: the Philox noise of (seed, offset, elem_base),
+// stream id offset + *step * 16 when `step` is given) -- exactly b200_sample_sumsq followed by b200_langevin_norm_sums,
+// same kernels, same summation order, with the per-sample scratch in static device memory.
+extern "C" int b200_langevin_norms_static(float* sums2, const float* score, const float* z, int B, long long n_per,
+                                          uint64_t seed, uint64_t offset, long long elem_base, const int* step,
+                                          cudaStream_t st) {
+  if (!sums2 || !score || B <= 0 || n_per <= 0 || (elem_base & 3) != 0) return B200_ERR_ARG;
+  if (B > B200_NORMS_STATIC_MAX_B) return B200_ERR_TOO_LARGE;      // beyond the static scratch: use the two-call form
+  float* scratch = nullptr;
+  if (int rc = norms_scratch_ptr(&scratch)) return rc;
+  float* ss_s = scratch;
+  float* ss_z = scratch + B200_NORMS_STATIC_MAX_B;
+  sumsq_kernel<<<B, 256, 0, st>>>(ss_s, ss_z, score, z, n_per, seed, offset, elem_base, step);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return -(1000 + (int)e);
+  norm_sums_kernel<<<1, 256, 0, st>>>(sums2, ss_s, ss_z, B);
+  B200_RETURN_LAST();
+}

@@ -76,6 +76,16 @@ int b200_ns_cip_advect(float* out, const float* field, const float* vel, long lo
 int b200_sample_sumsq(float* ss_score, float* ss_noise, const float* score, const float* z, int B, long long n_per,
                       uint64_t seed, uint64_t offset, long long elem_base, const int* step, cudaStream_t stream);
 int b200_langevin_norm_sums(float* sums2, const float* ss_score, const float* ss_noise, int B, cudaStream_t stream);
+/* NO COUNTERPART IN THE REFERENCE.  Allocation-free form of the two calls
+ * above for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it):
+ * sums2[0] = sum_b ||score_b||, sums2[1] = sum_b ||z_b|| with the per-sample [2][B] scratch in a file-scope static
+ * device array (128 KB, held by every GPU that loads the library until exit).  B <= 16384
+ * (b200_langevin_norms_static_max_batch()); larger B returns -4 ("size beyond the static scratch capacity").  Calls no
+ * cudaMalloc / cudaFree.  Every call shares the array, which keeps the last call's contents (nothing needs clearing:
+ * entries [0, B) are written before they are read); calls that overlap on the GPU (different streams) race. */
+int b200_langevin_norms_static_max_batch(void);
+int b200_langevin_norms_static(float* sums2, const float* score, const float* z, int B, long long n_per, uint64_t seed,
+                               uint64_t offset, long long elem_base, const int* step, cudaStream_t stream);
 int b200_sde_update(float* x, float* x_mean, const float* score, const float* z, const float* a, const float* b,
                     const float* c, const int* step, int langevin, const float* norm_sums, float inv_batch_total,
                     float snr, int B, long long n_per, uint64_t seed, uint64_t offset, long long elem_base,
