@@ -235,7 +235,7 @@ class Builder:
             gn.real = out
             self.emit("b200_gn_apply_stats", x, x.C, s1, t1, p2, c2, s2, t2, self.dt, self.B, HW, gn.groups,
                       self.lib.b200_gn_nsplit(self.B, HW), self.e.dev(gn.key + ".weight"), self.e.dev(gn.key + ".bias"),
-                      1e-6, 1, out)
+                      1e-6, 1, out, tag="%dx%d %d" % (x.H, x.W, gn.C))
         return gn.real
 
     def emit(self, name, *args, flops=0, tag=""):
@@ -267,7 +267,8 @@ class Builder:
             s1, t1 = tc.request_stats(self, x)
             s2, t2 = tc.request_stats(self, x2) if x2 is not None else (None, 0)
             self.emit("b200_gn_apply_stats", x, x.C, s1, t1, p2, c2, s2, t2, self.dt, self.B, HW, groups, ns,
-                      self.e.dev(key + ".weight"), self.e.dev(key + ".bias"), 1e-6, 1 if act else 0, out)
+                      self.e.dev(key + ".weight"), self.e.dev(key + ".bias"), 1e-6, 1 if act else 0, out,
+                      tag="%dx%d %d" % (x.H, x.W, C))
             self.rec("gn", x=x, x2=x2, out=out, key=key, groups=groups, act=act)
             return out
         part = self.f32(self.B * ns * groups * 2)
