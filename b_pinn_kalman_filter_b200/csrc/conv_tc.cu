@@ -949,6 +949,18 @@ extern "C" int b200_conv2d_tc_gn_supported(int C1, int C2, int B, int H, int W, 
   return (on && hp) ? 1 : 0;
 }
 
+// 1: ... and the fused form is the faster one for this shape (what the engine's planner asks).  Measured at B = 1024 and
+// B = 128 (profiles/r02_gn_fusion_shapes.txt): 256-wide pair tiles gain 4-9 % over conv + standalone GroupNorm; 128-wide
+// pair tiles LOSE 3-16 %: an N = 128 pair MMA already reads 96 of the 128 B/clk the SM's shared memory delivers (4 KB of
+// A + 2 KB of B per 64 clk) and the in-place transform adds ~40 B/clk (one 16-byte load and up to three stores per 8
+// channels of each of the 180 unique pixels of a stage) -- those convolutions become shared-memory-bandwidth bound.
+extern "C" int b200_conv2d_tc_gn_preferred(int C1, int C2, int B, int H, int W, int Cout, int ksize) {
+  if (!b200_conv2d_tc_gn_supported(C1, C2, B, H, W, Cout, ksize)) return 0;
+  int BN; bool hp;
+  conv_tc_variant(B, H, W, Cout, ksize, 0, BN, hp);
+  return BN == 256 ? 1 : 0;
+}
+
 static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
                           const float* temb, int temb_stride, const void* res, float out_scale, void* out,
                           int out_mode, const float* sample_mul, float* stats, const float* gn_coef, int B, int H, int W,

@@ -385,8 +385,10 @@ class ScoreEngine:
         self.dt = {"bf16": DT_BF16, "fp32": DT_F32}[precision]
         self.use_tc = bool(use_tensor_cores) and self.dt == DT_BF16
         self.fuse_gn_stats = True           # GroupNorm statistics as a by-product of the producing conv's epilogue
-        # GroupNorm + SiLU applied inside the consuming conv's operand pipeline (B200_FUSE_GN=0: A/B measurements)
-        self.fuse_gn_conv = os.environ.get("B200_FUSE_GN", "1") != "0"
+        # GroupNorm + SiLU applied inside the consuming conv's operand pipeline: True = where it is the faster form
+        # (b200_conv2d_tc_gn_preferred), "all" = wherever the fused kernel can run, False = never
+        # (B200_FUSE_GN=0 / all: A/B measurements)
+        self.fuse_gn_conv = {"0": False, "all": "all"}.get(os.environ.get("B200_FUSE_GN", "1"), True)
         self.gn_fused = 0
         self.workspace = Workspace(self.device)
         self.params = {}           # reference-layout fp32 tensors on device

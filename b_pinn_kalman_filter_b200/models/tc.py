@@ -18,6 +18,7 @@ _lib.register_signature("b200_gn_apply_stats", [c_vp, c_int, c_vp, c_int, c_vp, 
 _lib.register_signature("b200_gn_coef", [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_float,
                                         c_vp])
 _lib.register_signature("b200_conv2d_tc_gn_supported", [c_int] * 7)
+_lib.register_signature("b200_conv2d_tc_gn_preferred", [c_int] * 7)
 _lib.register_signature("b200_conv2d_tc_gn", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float,
                                               c_vp, c_vp, c_int, c_int, c_int, c_int, c_int])
 
@@ -45,7 +46,9 @@ def conv_gn_supported(b, x1, x2, out, ksize, stride, pad):
     if not (ENABLED and FUSE_GN) or ksize != 3 or stride != 1 or pad != (1, 1) or (out.H, out.W) != (x1.H, x1.W):
         return False
     c2 = x2.C if x2 is not None else 0
-    return bool(_lib.lib().b200_conv2d_tc_gn_supported(x1.C, c2, b.B, x1.H, x1.W, out.C, ksize))
+    # "all": every shape the fused kernel can run; otherwise only where it measured faster than conv + GroupNorm launch
+    fn = _lib.lib().b200_conv2d_tc_gn_supported if b.e.fuse_gn_conv == "all" else _lib.lib().b200_conv2d_tc_gn_preferred
+    return bool(fn(x1.C, c2, b.B, x1.H, x1.W, out.C, ksize))
 
 
 def emit_conv_gn(b, gn, w, bias, temb_ptr, res, out_scale, out, ksize, flops):

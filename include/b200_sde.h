@@ -150,6 +150,9 @@ int b200_conv2d_tc_stat_slots(int B, int H, int W);
 int b200_gn_coef(const float* st1, int T1, int C1, const float* st2, int T2, int C2, int B, int HW, int G,
                  const float* gamma, const float* beta, float eps, float* coef, cudaStream_t stream);
 int b200_conv2d_tc_gn_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize);
+/* 1 where the fused form is also the FASTER one (256-wide tiles; the 128-wide ones are shared-memory-bandwidth bound
+ * and lose to conv + standalone GroupNorm): what the engine's planner asks */
+int b200_conv2d_tc_gn_preferred(int C1, int C2, int B, int H, int W, int Cout, int ksize);
 int b200_conv2d_tc_gn(const void* x1, int C1, const void* x2, int C2, const float* gn_coef, const void* w,
                       const float* bias, const float* temb, int temb_stride, const void* res, float out_scale, void* out,
                       float* stats, int B, int H, int W, int Cout, int ksize, cudaStream_t stream);

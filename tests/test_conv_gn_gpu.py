@@ -113,7 +113,7 @@ def test_network_with_and_without_gn_fusion_is_bit_identical(cuda, B):
     xb = (torch.rand(B, 3, 32, 32, generator=g) * 1.5 - 0.25).to(cuda)
     lb = torch.exp(torch.rand(B, generator=g) * 8.5 - 4.6).to(cuda)
     outs, counts = [], []
-    for fuse in (False, True):
+    for fuse in (False, "all"):
         m = mutils.ScoreModel(cfg, device=cuda, precision="bf16", init=False)
         m.load_state_dict(sd)
         m.engine.fuse_gn_conv = fuse
