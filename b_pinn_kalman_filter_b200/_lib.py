@@ -35,6 +35,12 @@ _SIGNATURES = {
     "b200_sample_sumsq": [c_vp, c_vp, c_vp, c_vp, c_int, c_ll, c_u64, c_u64, c_ll, c_vp, c_vp],
     "b200_langevin_norm_sums": [c_vp, c_vp, c_vp, c_int, c_vp],
     "b200_langevin_norms_static_max_batch": [],
+    "b200_xchg_max_ranks": [],
+    "b200_xchg_alloc": [ctypes.POINTER(c_vp), ctypes.c_char_p],
+    "b200_xchg_open": [ctypes.c_char_p, ctypes.POINTER(c_vp)],
+    "b200_xchg_close": [c_vp],
+    "b200_xchg_free": [c_vp],
+    "b200_langevin_norm_sums_xchg": [c_vp, c_vp, c_vp, c_int, ctypes.POINTER(c_vp), c_int, c_int, c_vp],
     "b200_langevin_norms_static": [c_vp, c_vp, c_vp, c_int, c_ll, c_u64, c_u64, c_ll, c_vp, c_vp],
     "b200_sde_update": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_float, c_int, c_ll,
                         c_u64, c_u64, c_ll, c_vp],

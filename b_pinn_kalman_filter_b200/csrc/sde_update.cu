@@ -8,6 +8,8 @@
 // Langevin corrector derives b = eps, c = sqrt(2 eps) from batch-mean norms of s and z (sampling.py:276-278).
 // z is either supplied (parity mode: the caller's torch.randn) or generated in registers with Philox4x32-10.
 // HBM-bound: 12 B/element (read x, s; write x) + 4 B if z is read + 4 B if x_mean is written.
+#include <cstring>
+
 #include "common.cuh"
 #include "../../include/b200_sde.h"
 
@@ -54,15 +56,112 @@ __global__ void __launch_bounds__(256) sumsq_kernel(float* __restrict__ ss_s, fl
   if (ss_z) { float t = block_sum(az, red); if (threadIdx.x == 0) ss_z[b] = t; }
 }
 
-// sums[0] = sum_b sqrt(ss_s[b]),  sums[1] = sum_b sqrt(ss_z[b])   (single block; B is a few thousand at most)
+// sums[0] = sum_b sqrt(ss_s[b]),  sums[1] = sum_b sqrt(ss_z[b])   (single block; B is a few thousand at most).
+// The per-sample norms are accumulated as EXACT fixed-point integers (2^-30 resolution, int64): integer addition is
+// associative, so the total does not depend on the order of summation -- nor on how the batch is cut into shards.  A
+// batch-sharded run that adds its ranks' integer partials (norm_sums_xchg_kernel below) therefore takes bit for bit the
+// Langevin step size of the unsharded batch (reference sampling.py:276-278 averages the norms over the WHOLE batch).
+// Range: sum_b ||.||_2 < 2^33 = 8.6e9 (C3: 1024 x 5.5e3; C5: 64 x 4.4e4).
+#define B200_NORM_FIX_SCALE 1073741824.0   /* 2^30 */
+__device__ __forceinline__ long long norm_to_fix(float ss) { return __double2ll_rn((double)sqrtf(ss) * B200_NORM_FIX_SCALE); }
+__device__ __forceinline__ float fix_to_norm(long long v) { return (float)((double)v * (1.0 / B200_NORM_FIX_SCALE)); }
+
+// Block-wide sum of int64; every thread gets the result.  `red` is >= 32 long longs of shared memory.
+__device__ __forceinline__ long long block_sum_ll(long long v, long long* red) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int nw = (blockDim.x + 31) >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if (lane == 0) red[wid] = v;
+  __syncthreads();
+  long long r = (lane < nw) ? red[lane] : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+  return r;
+}
+
+__device__ __forceinline__ void local_norm_sums_fix(const float* __restrict__ ss_s, const float* __restrict__ ss_z, int B,
+                                                    long long* red, long long& a, long long& c) {
+  a = 0; c = 0;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) { a += norm_to_fix(ss_s[i]); c += norm_to_fix(ss_z[i]); }
+  a = block_sum_ll(a, red);
+  c = block_sum_ll(c, red);
+}
+
 __global__ void __launch_bounds__(256) norm_sums_kernel(float* __restrict__ sums, const float* __restrict__ ss_s,
                                                         const float* __restrict__ ss_z, int B) {
-  __shared__ float red[32];
-  float a = 0.f, c = 0.f;
-  for (int i = threadIdx.x; i < B; i += blockDim.x) { a += sqrtf(ss_s[i]); c += sqrtf(ss_z[i]); }
-  a = block_sum(a, red);
-  c = block_sum(c, red);
-  if (threadIdx.x == 0) { sums[0] = a; sums[1] = c; }
+  __shared__ long long red[32];
+  long long a, c;
+  local_norm_sums_fix(ss_s, ss_z, B, red, a, c);
+  if (threadIdx.x == 0) { sums[0] = fix_to_norm(a); sums[1] = fix_to_norm(c); }
+}
+
+// ---- the same reduction fused with its cross-GPU exchange over peer memory (NVLink P2P) ----------------------------
+// Replaces norm_sums_kernel + an 8-byte ncclAllReduce between the corrector's forward and its update.  Every rank owns
+// a slot table in ITS OWN memory, [2 parities][B200_XCHG_MAX_RANKS] slots of {int64 partial[2], epoch}; the peers map
+// it through CUDA IPC.  One call = one epoch e (a counter in local memory, advanced by the kernel, so a captured CUDA
+// graph replays correctly): the block reduces its shard, stores its two partials into slot [e & 1][rank] of EVERY rank
+// (payload, then the epoch with release semantics at system scope), then waits until the `world` slots of parity e & 1
+// in its own table carry epoch e and adds them in rank order.  Two parities suffice: a rank can only reach epoch e + 2
+// (which overwrites parity e & 1) after every peer has published e + 1, i.e. after that peer's stream has finished
+// reading epoch e.  No host involvement, no extra launch.  A peer that never arrives (died) does not hang the GPU: after
+// B200_XCHG_TIMEOUT_NS the sums become NaN (the sampler's finiteness check trips).
+#define B200_XCHG_MAX_RANKS 8
+#define B200_XCHG_TIMEOUT_NS 10000000000ull
+struct XchgSlot { long long v[2]; unsigned int epoch; unsigned int pad[3]; };      // 32 bytes
+struct XchgTable { XchgSlot slot[2][B200_XCHG_MAX_RANKS]; unsigned int epoch_ctr; unsigned int pad[7]; };
+struct XchgPeers { XchgTable* table[B200_XCHG_MAX_RANKS]; int world, rank; };
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__global__ void __launch_bounds__(256) norm_sums_xchg_kernel(float* __restrict__ sums, const float* __restrict__ ss_s,
+                                                             const float* __restrict__ ss_z, int B, XchgPeers P) {
+  __shared__ long long red[32];
+  __shared__ long long got[B200_XCHG_MAX_RANKS][2];
+  __shared__ int failed;
+  XchgTable* mine = P.table[P.rank];
+  const unsigned int e = *(volatile unsigned int*)&mine->epoch_ctr + 1;   // read by all before thread 0 advances it
+  if (threadIdx.x == 0) failed = 0;
+  long long a, c;
+  local_norm_sums_fix(ss_s, ss_z, B, red, a, c);        // (contains __syncthreads)
+  const int r = threadIdx.x;
+  if (r < P.world) {
+    XchgSlot* dst = &P.table[r]->slot[e & 1][P.rank];   // my slot in rank r's table (r == rank: my own memory)
+    volatile long long* pv = dst->v;
+    pv[0] = a; pv[1] = c;
+    st_release_sys(&dst->epoch, e);
+    const XchgSlot* src = &mine->slot[e & 1][r];
+    const unsigned long long t0 = global_ns();
+    bool ok = true;
+    while (ld_acquire_sys(&src->epoch) != e) {
+      if (global_ns() - t0 > B200_XCHG_TIMEOUT_NS) { ok = false; break; }
+      __nanosleep(100);
+    }
+    const volatile long long* sv = src->v;
+    got[r][0] = sv[0]; got[r][1] = sv[1];
+    if (!ok) failed = 1;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long ta = 0, tc = 0;
+    for (int i = 0; i < P.world; ++i) { ta += got[i][0]; tc += got[i][1]; }
+    sums[0] = failed ? __int_as_float(0x7fc00000) : fix_to_norm(ta);
+    sums[1] = failed ? __int_as_float(0x7fc00000) : fix_to_norm(tc);
+    mine->epoch_ctr = e;
+  }
 }
 
 struct UpdArgs {
@@ -203,6 +302,62 @@ extern "C" int b200_fill_normal(float* out, long long total, float scale, uint64
 extern "C" int b200_step_advance(int* step, int delta, cudaStream_t st) {
   if (!step) return B200_ERR_ARG;
   step_advance_kernel<<<1, 32, 0, st>>>(step, delta);
+  B200_RETURN_LAST();
+}
+
+// ---- peer exchange set-up (once per sharded sampler; the only allocation of the exchange path) -----------------------
+extern "C" int b200_xchg_max_ranks(void) { return B200_XCHG_MAX_RANKS; }
+
+// Allocates this rank's slot table (zeroed) and returns its CUDA IPC handle (64 bytes) for the peers to open.
+extern "C" int b200_xchg_alloc(void** table, unsigned char* handle64) {
+  if (!table || !handle64) return B200_ERR_ARG;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  void* p = nullptr;
+  cudaError_t e = cudaMalloc(&p, sizeof(XchgTable));
+  if (e != cudaSuccess) return -(1000 + (int)e);
+  e = cudaMemset(p, 0, sizeof(XchgTable));
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  cudaIpcMemHandle_t h;
+  if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) { cudaFree(p); return -(1000 + (int)e); }
+  memcpy(handle64, &h, 64);
+  *table = p;
+  return B200_OK;
+}
+// Maps a peer's slot table (same node, P2P-capable pair of GPUs) into this process.
+extern "C" int b200_xchg_open(const unsigned char* handle64, void** table) {
+  if (!table || !handle64) return B200_ERR_ARG;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  void* p = nullptr;
+  cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+  if (e != cudaSuccess) { cudaGetLastError(); return -(1000 + (int)e); }
+  *table = p;
+  return B200_OK;
+}
+extern "C" int b200_xchg_close(void* peer_table) {
+  if (!peer_table) return B200_OK;
+  cudaError_t e = cudaIpcCloseMemHandle(peer_table);
+  return e == cudaSuccess ? B200_OK : -(1000 + (int)e);
+}
+extern "C" int b200_xchg_free(void* table) {
+  if (!table) return B200_OK;
+  cudaError_t e = cudaFree(table);
+  return e == cudaSuccess ? B200_OK : -(1000 + (int)e);
+}
+
+// b200_langevin_norm_sums for a batch-sharded run: sums2 = the GLOBAL sums over all `world` ranks' samples, exchanged
+// through the peers' slot tables (tables[r] = rank r's table as mapped in THIS process, tables[rank] = the local one).
+// Every rank must make the same sequence of calls.  Graph-capturable (no host synchronisation, fixed arguments).
+extern "C" int b200_langevin_norm_sums_xchg(float* sums2, const float* ss_s, const float* ss_z, int B,
+                                            void* const* tables, int world, int rank, cudaStream_t st) {
+  if (!sums2 || !ss_s || !ss_z || B <= 0 || !tables || world < 1 || world > B200_XCHG_MAX_RANKS || rank < 0 || rank >= world)
+    return B200_ERR_ARG;
+  XchgPeers P;
+  for (int r = 0; r < B200_XCHG_MAX_RANKS; ++r) P.table[r] = r < world ? static_cast<XchgTable*>(tables[r]) : nullptr;
+  for (int r = 0; r < world; ++r) if (!P.table[r]) return B200_ERR_ARG;
+  P.world = world; P.rank = rank;
+  norm_sums_xchg_kernel<<<1, 256, 0, st>>>(sums2, ss_s, ss_z, B, P);
   B200_RETURN_LAST();
 }
 

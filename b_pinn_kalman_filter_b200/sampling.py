@@ -16,6 +16,7 @@ How it runs:
 import abc
 import functools
 import math
+import os
 
 import numpy as np
 import torch
@@ -419,7 +420,19 @@ class FusedPCLoop:
         self.elem_base = sharding.philox_element_base(rank_offset, self.n_per)
         self.seed = _SEED[0] if seed is None else seed
         self.snr = float(snr)
-        self.use_graph = use_graph and NOISE_FN is None and process_group is None
+        self.use_graph = use_graph and NOISE_FN is None
+        # sharded Langevin: the two batch-mean norms cross the GPUs inside the reducing kernel over NVLink peer memory
+        # (csrc/sde_update.cu norm_sums_xchg_kernel) -- no NCCL call in the step, so the step stays graph-capturable;
+        # if the peers' memory cannot be mapped every rank falls back to an eager NCCL all-reduce of the 8 bytes
+        self.xchg = None
+        self.world = 1
+        if process_group is not None:
+            import torch.distributed as dist
+            self.world = dist.get_world_size(process_group)
+        if self.world > 1 and corrector is LangevinCorrector and n_steps > 0:
+            if os.environ.get("B200_PEER_XCHG", "1") != "0":
+                x = sharding.PeerExchange(process_group, self.dev)
+                self.xchg = x if x.ok else None
         N = sde.N
         dev = self.dev
         t = torch.linspace(sde.T, eps, N, device=dev)
@@ -490,9 +503,14 @@ class FusedPCLoop:
             _lib.check(lib.b200_sample_sumsq(_lib.ptr(self.ss[0]), _lib.ptr(self.ss[1]), _lib.ptr(score), zp, B, n_per,
                                              self.seed, off, self.elem_base, _lib.ptr(self.step_dev), st),
                        "b200_sample_sumsq")
-            _lib.check(lib.b200_langevin_norm_sums(_lib.ptr(self.sums), _lib.ptr(self.ss[0]), _lib.ptr(self.ss[1]), B,
-                                                   st), "b200_langevin_norm_sums")
-            sharding.allreduce_norm_sums(self.sums, self.pg)
+            if self.xchg is not None:
+                _lib.check(lib.b200_langevin_norm_sums_xchg(_lib.ptr(self.sums), _lib.ptr(self.ss[0]),
+                                                            _lib.ptr(self.ss[1]), B, self.xchg.tables, self.xchg.world,
+                                                            self.xchg.rank, st), "b200_langevin_norm_sums_xchg")
+            else:
+                _lib.check(lib.b200_langevin_norm_sums(_lib.ptr(self.sums), _lib.ptr(self.ss[0]), _lib.ptr(self.ss[1]),
+                                                       B, st), "b200_langevin_norm_sums")
+                sharding.allreduce_norm_sums(self.sums, self.pg)
             _lib.check(lib.b200_sde_update(_lib.ptr(self.x), _lib.ptr(self.x_mean), _lib.ptr(score), zp,
                                            _lib.ptr(self.corr[1]), None, None, _lib.ptr(self.step_dev), 1,
                                            _lib.ptr(self.sums), 1.0 / self.total_batch, self.snr, B, n_per, self.seed,
@@ -561,7 +579,8 @@ class FusedPCLoop:
         return n
 
     def _graphable(self):
-        return (self.use_graph and NOISE_FN is None and self.pg is None and self.scaled is None
+        needs_nccl = self.world > 1 and self.corr is not None and self.corr[0] == "langevin" and self.xchg is None
+        return (self.use_graph and NOISE_FN is None and not needs_nccl and self.scaled is None
                 and self.n_steps + 1 <= 16)
 
     def run(self, n_iters):

@@ -40,6 +40,53 @@ def allreduce_norm_sums(sums, group):
     return sums
 
 
+class PeerExchange:
+    """Slot tables of b200_langevin_norm_sums_xchg for one process group (all ranks on ONE node, <= 8 GPUs): every
+    rank allocates its table, the CUDA IPC handles travel through `all_gather_object`, every rank maps its peers'
+    tables.  `ok` is a COLLECTIVE verdict (all ranks succeeded) so that the ranks never disagree on which path they
+    take; on False the sampler keeps the NCCL all-reduce.  The 1 KB table is deliberately never freed: a peer's kernel
+    may still be writing into it when this object dies."""
+
+    def __init__(self, group, device):
+        import ctypes
+        import torch.distributed as dist
+        from . import _lib
+        self.lib = _lib.lib()
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.ok, self.tables, self.why = False, None, ""
+        device = torch.device(device)
+        rc, raw, local = -1, b"", ctypes.c_void_p()
+        if device.type == "cuda" and self.world <= self.lib.b200_xchg_max_ranks():
+            with torch.cuda.device(device):
+                buf = ctypes.create_string_buffer(64)
+                rc = self.lib.b200_xchg_alloc(ctypes.byref(local), buf)
+                raw = buf.raw
+        handles = [None] * self.world
+        dist.all_gather_object(handles, (rc, raw), group=group)
+        ok = all(h[0] == 0 for h in handles)
+        ptrs = []
+        if ok:
+            with torch.cuda.device(device):
+                for r, (_, h) in enumerate(handles):
+                    if r == self.rank:
+                        ptrs.append(local.value)
+                        continue
+                    p = ctypes.c_void_p()
+                    rc = self.lib.b200_xchg_open(h, ctypes.byref(p))
+                    if rc != 0:
+                        ok, self.why = False, "cudaIpcOpenMemHandle failed for rank %d (code %d)" % (r, rc)
+                        break
+                    ptrs.append(p.value)
+        else:
+            self.why = "slot table allocation failed or more than 8 ranks"
+        flag = torch.tensor([1 if ok else 0], device=device if device.type == "cuda" else "cpu", dtype=torch.int32)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        self.ok = bool(flag.item())
+        if self.ok:
+            self.tables = (ctypes.c_void_p * self.world)(*ptrs)
+
+
 def langevin_step_size(sums, total_batch, snr, alpha):
     """step = 2 alpha (snr * mean||z|| / mean||grad||)^2 from the GLOBAL sums (sampling.py:276-278); the same
     expression the update kernel evaluates (csrc/sde_update.cu)."""
@@ -93,4 +140,4 @@ def philox_element_base(rank_offset, elems_per_sample):
 
 
 __all__ = ["shard_range", "local_norm_sums", "allreduce_norm_sums", "langevin_step_size", "gather_samples",
-           "max_over_ranks", "philox_element_base"]
+           "max_over_ranks", "philox_element_base", "PeerExchange"]

@@ -76,6 +76,20 @@ int b200_ns_cip_advect(float* out, const float* field, const float* vel, long lo
 int b200_sample_sumsq(float* ss_score, float* ss_noise, const float* score, const float* z, int B, long long n_per,
                       uint64_t seed, uint64_t offset, long long elem_base, const int* step, cudaStream_t stream);
 int b200_langevin_norm_sums(float* sums2, const float* ss_score, const float* ss_noise, int B, cudaStream_t stream);
+/* Batch-sharded runs (one process per GPU): the reference averages the Langevin norms over the WHOLE batch
+ * (sampling.py:276-278), so the ranks' partial sums must meet.  b200_langevin_norm_sums_xchg is b200_langevin_norm_sums
+ * fused with that exchange over NVLink peer memory: the reducing block stores its two (exact, fixed-point int64)
+ * partials into every peer's CUDA-IPC-mapped slot table with a release store, waits for the peers' slots of the same
+ * epoch and adds them in rank order -- no NCCL call, no host involvement, graph-capturable, and bit-identical to the
+ * unsharded batch's sums.  b200_xchg_alloc / _open / _close / _free set the slot tables up once per sampler
+ * (world <= b200_xchg_max_ranks() = 8 GPUs of one node); every rank must make the same sequence of calls. */
+int b200_xchg_max_ranks(void);
+int b200_xchg_alloc(void** table, unsigned char* handle64);
+int b200_xchg_open(const unsigned char* handle64, void** table);
+int b200_xchg_close(void* peer_table);
+int b200_xchg_free(void* table);
+int b200_langevin_norm_sums_xchg(float* sums2, const float* ss_score, const float* ss_noise, int B, void* const* tables,
+                                 int world, int rank, cudaStream_t stream);
 /* NO COUNTERPART IN THE REFERENCE.  Allocation-free form of the two calls
  * above for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it):
  * sums2[0] = sum_b ||score_b||, sums2[1] = sum_b ||z_b|| with the per-sample [2][B] scratch in a file-scope static
