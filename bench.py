@@ -36,8 +36,11 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch-per-gpu", type=int, default=0, help="default: 1024 at N=1, 1024/N otherwise ... see --scaling")
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="weak: every GPU samples --batch-per-gpu (default 1024) images; strong: 1024 images total")
+    ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                    help="strong (default, BASELINE.json configs[2]): 1024 images TOTAL, 1024/N per GPU; weak: every GPU "
+                         "samples 1024 images (reported as the secondary `weak` object of the strong line anyway)")
+    ap.add_argument("--no-weak", action="store_true", help="skip the secondary weak-scaling measurement at N > 1")
+    ap.add_argument("--no-ref-gpu", action="store_true", help="skip the reference-ops-on-this-GPU leg (aux.reference_gpu)")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--e2e-steps", type=int, default=0, help="PC steps of the end-to-end API run (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -156,15 +159,16 @@ def run_reference(a):
     steps = max(1, a.steps)
     warm = a.warmup
     t0 = time.perf_counter()
-    s_per_step, b = cpu_pc_steps(a.cpu_batch, min(steps, 4), os.cpu_count() or 1)
+    n_cpu = min(max(steps, 1), 20)
+    s_per_step, b = cpu_pc_steps(a.cpu_batch, n_cpu, os.cpu_count() or 1)
     val = b / (s_per_step * N_STEPS)
     line = {"impl": "reference", "metric": "PC samples/s (NCSN++ 32x32, 1000 steps)", "value": val, "unit": "samples/s",
             "n_gpus": a.gpus, "steps": a.steps, "warmup": warm, "ms_per_step": s_per_step * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "C3 cifar10 NCSN++ VE PC sampler (reverse_diffusion + langevin, snr 0.16), N=1000",
-                       "batch": b, "timed_pc_steps": min(steps, 4)},
+                       "batch": b, "timed_pc_steps": n_cpu},
             "cpu_baseline": {"value": val, "unit": "samples/s", "cores": os.cpu_count() or 1, "kind": "port",
-                             "sample": "%d PC steps at batch %d on the host, per-step time x 1000" % (min(steps, 4), b)},
+                             "sample": "%d PC steps at batch %d on the host, per-step time x 1000" % (n_cpu, b)},
             "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
     emit(line)
@@ -282,6 +286,95 @@ def other_config_measurements(dev, timeit):
     return res
 
 
+def reference_gpu_leg(dev, our_fwd_ms, B, precision):
+    """The "kernel to beat" (SURVEY 2b / BASELINE.md section 4): what the reference's own GPU path costs on THIS B200.
+    (i) its score-network forward = the same torch ops (F.conv2d / group_norm / einsum / silu ...) on cuDNN / cuBLAS
+        sm_100 kernels, run through the oracle's functional restatement of NCSNpp.forward (models/ncsnpp.py:232-381) on
+        the device, in fp32, TF32 and bf16 autocast, at the bench's batch;
+    (ii) its own CUDA extensions (oracle/_ref, built from the unmodified op/*.cu for sm_100) at the aux shapes.
+    Outside the timed `value`; oracle/ is used here as the thing measured AGAINST, never as the product."""
+    import torch
+    from oracle import build_ref_ext, score_net_ref, weights
+    from b_pinn_kalman_filter_b200 import configs, op
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    from b_pinn_kalman_filter_b200.models.engine import parameter_spec
+    out = {}
+
+    def timeit(fn, iters):
+        fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+
+    try:
+        cfg = configs.get_config(CONFIG)
+        spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+        sd = weights.trained_like_state_dict(spec, cfg, seed=42)
+        net = score_net_ref.RefScoreNet(cfg, sd, device=dev)
+        x = torch.rand(B, 3, 32, 32, device=dev)
+        lab = torch.exp(torch.rand(B, device=dev) * 8.5 - 4.6)
+        saved = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.benchmark)
+        torch.backends.cudnn.benchmark = True
+        modes = {}
+        try:
+            for tag, tf32, autocast in (("fp32", False, False), ("tf32", True, False), ("bf16_autocast", True, True)):
+                torch.backends.cudnn.allow_tf32 = tf32
+                torch.backends.cuda.matmul.allow_tf32 = tf32
+                with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                    ms = timeit(lambda: net(x, lab), 3 if not tf32 else 5)
+                modes[tag] = {"ms_per_forward": ms, "speedup_ours_vs_reference": ms / our_fwd_ms}
+        finally:
+            torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.benchmark = saved
+        out["score_net_forward"] = {"batch": B, "ours_ms_per_forward": our_fwd_ms, "ours_precision": precision,
+                                    "reference_ops": "torch %s F.conv2d / group_norm / einsum on cuDNN + cuBLAS (sm_100), "
+                                                     "eager, as the reference runs them" % torch.__version__, **modes}
+        del net, x
+        torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001 -- a side measurement must never take the bench line down
+        out["score_net_forward"] = {"unavailable": repr(e)[:200]}
+
+    try:
+        ext = build_ref_ext.load_ext("upfirdn2d")
+        if ext is None:
+            raise RuntimeError("oracle/_ref/upfirdn2d not built")
+        k1 = torch.tensor([1., 3., 3., 1.], device=dev)
+        k = torch.outer(k1, k1)
+        k = k / k.sum()
+        xs = torch.randn(8 * 128, 256, 256, 1, device=dev)
+        from b_pinn_kalman_filter_b200.op.upfirdn2d import _launch
+        nb = 4 * (xs.numel() + xs.numel() // 4)
+        ref_ms = timeit(lambda: ext.upfirdn2d(xs, k, 1, 1, 2, 2, 1, 1, 1, 1), 10)
+        xp = xs.view(-1, 256, 256)
+        our_ms = timeit(lambda: _launch(xp, k, (1, 1), (2, 2), (1, 1, 1, 1)), 10)
+        out["upfirdn2d_down2"] = {"shape": "[8x128,256,256] -> [.,128,128] fp32", "reference_kernel_ms": ref_ms,
+                                  "reference_kernel_GBps": nb / ref_ms / 1e6, "ours_ms": our_ms,
+                                  "ours_GBps": nb / our_ms / 1e6, "speedup": ref_ms / our_ms,
+                                  "reference_kernel": "op/upfirdn2d_kernel.cu:107-207 rebuilt for sm_100 (oracle/_ref)"}
+        del xs, xp
+        ext = build_ref_ext.load_ext("fused")
+        if ext is None:
+            raise RuntimeError("oracle/_ref/fused not built")
+        xa = torch.randn(128, 128, 32, 32, device=dev)
+        bias = torch.randn(128, device=dev)
+        empty = xa.new_empty(0)
+        ref_ms = timeit(lambda: ext.fused_bias_act(xa, bias, empty, 3, 0, 0.2, 2 ** 0.5), 20)
+        our_ms = timeit(lambda: op.fused_leaky_relu(xa, bias, 0.2, 2 ** 0.5), 20)
+        nb = 8 * xa.numel()
+        out["fused_bias_act"] = {"shape": "[128,128,32,32] fp32", "reference_kernel_ms": ref_ms,
+                                 "reference_kernel_GBps": nb / ref_ms / 1e6, "ours_ms": our_ms,
+                                 "ours_GBps": nb / our_ms / 1e6, "speedup": ref_ms / our_ms,
+                                 "note": "ours includes the python wrapper's output allocation",
+                                 "reference_kernel": "op/fused_bias_act_kernel.cu:18-49 rebuilt for sm_100 (oracle/_ref)"}
+    except Exception as e:  # noqa: BLE001
+        out["reference_extensions"] = {"unavailable": repr(e)[:200]}
+    return out
+
+
 def run_b200(a):
     import torch
     import torch.distributed as dist
@@ -344,6 +437,29 @@ def run_b200(a):
     total_B = B * world
     value = total_B / (ms_per_step * 1e-3 * N_STEPS)
 
+    # ---- secondary: weak scaling (1024 images on EVERY GPU) beside the strong headline ---------------------------
+    weak = None
+    if world > 1 and a.scaling == "strong" and not a.no_weak and not a.batch_per_gpu:
+        loop_w = sampling.FusedPCLoop(model, sde, (TOTAL_BATCH, 3, 32, 32), sampling.ReverseDiffusionPredictor,
+                                      sampling.LangevinCorrector, cfg.sampling.snr, cfg.sampling.n_steps_each, False, True,
+                                      1e-5, process_group=pg, rank_offset=rank * TOTAL_BATCH,
+                                      total_batch=TOTAL_BATCH * world, seed=1234)
+        loop_w.reset(torch.randn((TOTAL_BATCH, 3, 32, 32), device=dev) * sde.sigma_max)
+        loop_w.run(max(a.warmup, 3))
+        barrier()
+        w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0.record()
+        loop_w.run(a.steps)
+        w1.record()
+        barrier()
+        tw = torch.tensor([w0.elapsed_time(w1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+        wms = float(tw.item()) / a.steps
+        weak = {"value": TOTAL_BATCH * world / (wms * 1e-3 * N_STEPS), "unit": "samples/s", "ms_per_step": wms,
+                "batch_per_gpu": TOTAL_BATCH, "global_batch": TOTAL_BATCH * world, "scaling": "weak",
+                "graph_replay": loop_w.graph is not None}
+        del loop_w
+
     # ---- per-kernel breakdown of one score-net forward (CUDA events around every launch) -----------------------
     plan = loop.plan
     torch.cuda.synchronize()
@@ -353,6 +469,11 @@ def run_b200(a):
     top = max(table, key=lambda n: table[n][1])
     dom = max(conv_names, key=lambda n: table[n][1]) if conv_names else top
     n_l, d_ms, d_fl = table[dom]
+    if dom.startswith("b200_conv2d_tc"):
+        # one kernel template (conv_tc_kernel<...>) behind three entry points: plain, GroupNorm-fused input, stride 2
+        fam = [n for n in table if n.startswith("b200_conv2d_tc")]
+        n_l, d_ms, d_fl = (sum(table[n][i] for n in fam) for i in range(3))
+        dom = "b200_conv2d_tc"
     achieved = d_fl / (d_ms * 1e-3) / 1e12 if d_ms > 0 else 0.0
     # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture of this command
     # (profiles/summarize_ncu.py full ...); null when no capture is committed
@@ -408,7 +529,10 @@ def run_b200(a):
                        "value_definition": "global_batch / (measured s per PC step x 1000 PC steps)",
                        "l2": "activations per forward (>1 GB) exceed the 126 MB L2; no flush needed",
                        "weights": "random init seed 42 (init_scale=0 layers drawn at scale 1), Philox noise on device",
-                       "parallelism": "dp%d (batch shards, 8-byte all-reduce per Langevin step)" % world},
+                       "parallelism": "dp%d (batch shards; the two Langevin norm sums cross the GPUs inside the reducing "
+                                      "kernel over NVLink peer memory%s)" % (world, "" if loop.xchg is not None or world == 1
+                                                                             else " -- UNAVAILABLE here: NCCL all-reduce"),
+                       "graph_replay": loop.graph is not None},
             "score_evals_per_s": total_B * loop.forwards_per_step / (ms_per_step * 1e-3),
             "model_tflops": plan.flops() * loop.forwards_per_step * world / (ms_per_step * 1e-3) / 1e12,
             "gpu_launches": launches, "finite": finite and e2e_finite,
@@ -418,11 +542,15 @@ def run_b200(a):
                     "pc_steps_run": e2e_steps, "seconds": e2e_s, "nfe": nfe,
                     "api": "sampling.get_pc_sampler(VESDE(N=%d), ...)(model): pinned-host prior -> H2D, %d PC steps, "
                            "samples -> D2H; scaled to 1000 steps" % (e2e_steps, e2e_steps)}}
+    if weak is not None:
+        line["weak"] = weak
     if rank == 0:
         if not a.no_aux:
             line["aux"] = aux_measurements(dev, pk)
+            if not a.no_ref_gpu and world == 1:
+                line["aux"]["reference_gpu"] = reference_gpu_leg(dev, fwd_ms, B, a.precision)
         if not a.no_cpu_baseline and world == 1:
-            line["cpu_baseline"] = cpu_baseline_obj(a.cpu_batch, 2)
+            line["cpu_baseline"] = cpu_baseline_obj(a.cpu_batch, 20)      # >= 20 PC steps
         elif not a.no_cpu_baseline:
             line["cpu_baseline"] = {"value": None, "unit": "samples/s", "cores": os.cpu_count(), "kind": "port",
                                     "sample": "timed at N=1 only"}
