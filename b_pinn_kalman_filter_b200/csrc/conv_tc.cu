@@ -34,6 +34,8 @@ constexpr int TC_THREADS = 320;
 struct ConvTcParams {
   int B, H, W;                  // activation extent (stride 1: output extent too)
   int C1, C2, Cout;             // Cout = channels of the output tensor (multiple of BN)
+  int C3, C4;                   // shortcut sources (0 = none): extra K blocks at the CENTRE tap -- the 1x1 `Conv_2(x)` of a
+                                // residual block folded into Conv_1's K loop; weights [Cout][taps*(C1+C2) + C3 + C4]
   int taps_w, pad, stride;      // KW (1 or 3) -- KH == KW; pad = KW / 2 (0 for the stride-2 VALID convs)
   int TW, TH, TB;               // tile box: TW * TH * TB == 128
   int tiles_w, tiles_h;         // M tiles per image row / per image column (TB == 1), else 1
@@ -161,7 +163,8 @@ template <int BN, int EPI, bool HALO = false, bool DS = false, bool PAIR = false
 __global__ void __launch_bounds__(TC_THREADS + (HALO ? 32 : 0) + (GNF ? 32 * TC_XF_WARPS : 0), 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant__ CUtensorMap mapA2,
                const __grid_constant__ CUtensorMap mapW, const __grid_constant__ CUtensorMap mapOut,
-               const __grid_constant__ CUtensorMap mapRes, const ConvTcParams p) {
+               const __grid_constant__ CUtensorMap mapRes, const __grid_constant__ CUtensorMap mapX1,
+               const __grid_constant__ CUtensorMap mapX2, const ConvTcParams p) {
   using S = typename TcSmemSel<BN, HALO, DS, PAIR>::type;
   static_assert(!PAIR || (EPI == 0 && ((BN == 256 && !DS) || (BN == 128 && HALO))), "pair variants");
   static_assert(!GNF || (HALO && PAIR), "GroupNorm-fused operand pipeline: halo + pair variants only");
@@ -187,7 +190,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
   const int Ctot = p.C1 + p.C2;
   const int kb_per_tap = Ctot / TC_BK;
   const int taps = p.taps_w * p.taps_w;
-  const int num_kb = taps * kb_per_tap;
+  const int kb_extra = (p.C3 + p.C4) / TC_BK;            // shortcut K blocks (centre tap only)
+  const int num_kb = taps * kb_per_tap + (HALO ? 0 : kb_extra);
   const int num_tiles = p.num_m * p.num_n;
   // work items: tiles, round robin over CTAs; PAIR: pairs of M tiles (2 pm, 2 pm + 1), round robin over CTA pairs
   const int tile_first = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
@@ -269,6 +273,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             }
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
+          // shortcut K blocks: ONE box (the centre column shift; its row 1 is the centre tap) of the shortcut source
+          for (int kx = 0; kx < kb_extra; ++kx) {
+            mbar_wait(empty_bar(stage), phase ^ 1);
+            if (elected) {
+              const uint32_t sa = base + stage * S::A_BYTES + S::BOX_BYTES;
+              const int c = kx * TC_BK;
+              if constexpr (PAIR && !GNF) {
+                const uint32_t lbar = mapa_cta(full_bar(stage), 0);
+                if (cta_rank == 0) mbar_expect_tx(full_bar(stage), 2 * S::BOX_BYTES);
+                if (c < p.C3) tma_load_4d_2sm(sa, &mapX1, lbar, c, w0, h0 - 1, b0);
+                else tma_load_4d_2sm(sa, &mapX2, lbar, c - p.C3, w0, h0 - 1, b0);
+              } else {
+                mbar_expect_tx(full_bar(stage), S::BOX_BYTES);
+                if (c < p.C3) tma_load_4d(sa, &mapX1, full_bar(stage), c, w0, h0 - 1, b0);
+                else tma_load_4d(sa, &mapX2, full_bar(stage), c - p.C3, w0, h0 - 1, b0);
+              }
+            }
+            if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
+          }
         } else {
         for (int tap = 0; tap < taps; ++tap) {
           const int r = tap / p.taps_w, s = tap - r * p.taps_w;
@@ -293,6 +316,26 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
             }
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
+        }
+        for (int kx = 0; kx < kb_extra; ++kx) {          // shortcut K blocks: centre tap of the shortcut source
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          if (elected) {
+            const uint32_t sa = base + stage * S::STAGE_BYTES, sb = sa + S::A_BYTES;
+            const int c = kx * TC_BK;
+            if constexpr (PAIR) {
+              const uint32_t lbar = mapa_cta(full_bar(stage), 0);
+              if (cta_rank == 0) mbar_expect_tx(full_bar(stage), 2 * S::STAGE_BYTES);
+              if (c < p.C3) tma_load_4d_2sm(sa, &mapX1, lbar, c, w0 * p.stride, h0 * p.stride, b0);
+              else tma_load_4d_2sm(sa, &mapX2, lbar, c - p.C3, w0 * p.stride, h0 * p.stride, b0);
+              tma_load_2d_2sm(sb, &mapW, lbar, taps * Ctot + c, nt * BN + (int)cta_rank * 128);
+            } else {
+              mbar_expect_tx(full_bar(stage), S::STAGE_BYTES);
+              if (c < p.C3) tma_load_4d(sa, &mapX1, full_bar(stage), c, w0 * p.stride, h0 * p.stride, b0);
+              else tma_load_4d(sa, &mapX2, full_bar(stage), c - p.C3, w0 * p.stride, h0 * p.stride, b0);
+              tma_load_2d(sb, &mapW, full_bar(stage), taps * Ctot + c, nt * BN);
+            }
+          }
+          if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
         }
       }
@@ -327,6 +370,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               }
               if (++ws == NWS) { ws = 0; wphase ^= 1; }
             }
+          for (int kx = 0; kx < kb_extra; ++kx) {        // shortcut K blocks: one weight tile per ring stage
+            mbar_wait(wempty_bar(ws), wphase ^ 1);
+            if (elected) {
+              const uint32_t wdst = base + S::W_OFF + ws * (S::WGROUP * S::B_BYTES);
+              if constexpr (PAIR) {
+                const uint32_t lbar = mapa_cta(wfull_bar(ws), 0);
+                if (cta_rank == 0) mbar_expect_tx(wfull_bar(ws), 2 * S::B_BYTES);
+                tma_load_2d_2sm(wdst, &mapW, lbar, 9 * Ctot + kx * TC_BK, nt * BN + (int)cta_rank * (BN / 2));
+              } else {
+                mbar_expect_tx(wfull_bar(ws), S::B_BYTES);
+                tma_load_2d(wdst, &mapW, wfull_bar(ws), 9 * Ctot + kx * TC_BK, nt * BN);
+              }
+            }
+            if (++ws == NWS) { ws = 0; wphase ^= 1; }
+          }
         }
       }
     }
@@ -378,6 +436,25 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
               if (++ws == NWS) { ws = 0; wphase ^= 1; }
             }
             if (elected) { if constexpr (PAIR) tc_commit_2sm(empty_bar(stage)); else tc_commit(empty_bar(stage)); }
+            if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
+          }
+          for (int kx = 0; kx < kb_extra; ++kx) {        // shortcut K blocks: centre tap = box 1, row offset 1
+            if constexpr (GNF) mbar_wait_cluster(xf_bar(stage), phase); else mbar_wait(full_bar(stage), phase);
+            tc_fence_after();
+            mbar_wait(wfull_bar(ws), wphase);
+            tc_fence_after();
+            const uint64_t da = make_sw128_desc(base + stage * S::A_BYTES + S::BOX_BYTES + HALO_TW * 128);
+            const uint64_t db = make_sw128_desc(base + S::W_OFF + ws * (S::WGROUP * S::B_BYTES));
+            if (elected) {
+#pragma unroll
+              for (int k = 0; k < TC_BK / 16; ++k) {
+                if constexpr (PAIR) tc_mma_bf16_2sm(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, 1u);
+                else tc_mma_bf16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, 1u);
+              }
+              if constexpr (PAIR) { tc_commit_2sm(wempty_bar(ws)); tc_commit_2sm(empty_bar(stage)); }
+              else { tc_commit(wempty_bar(ws)); tc_commit(empty_bar(stage)); }
+            }
+            if (++ws == NWS) { ws = 0; wphase ^= 1; }
             if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
           }
         } else {
@@ -713,6 +790,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constant_
           if (lane == 0) mbar_arrive_cluster(mapa_cta(xf_bar(stage), 0));
           if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
         }
+        for (int kx = 0; kx < kb_extra; ++kx) {          // shortcut K blocks carry the RAW block input: pass them on
+          mbar_wait(full_bar(stage), phase);
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(mapa_cta(xf_bar(stage), 0));
+          if (++stage == S::STAGES) { stage = 0; phase ^= 1; }
+        }
       }
     }
   }
@@ -805,9 +888,11 @@ bool tile_box(int B, int H, int W, int& TW, int& TH, int& TB, int& tiles_w, int&
   return TB <= 256;
 }
 
+struct XMaps { CUtensorMap x1, x2; };     // shortcut sources (unused copies of the A map when p.C3 + p.C4 == 0)
+
 template <int BN, int EPI, bool HALO = false, bool DS = false>
 int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
-           const ConvTcParams& p, cudaStream_t st) {
+           const ConvTcParams& p, cudaStream_t st, const XMaps* xm = nullptr) {
   // residual tiles are fetched with the geometry of the output boxes (same tensor shape, other base pointer)
   CUtensorMap rm = om;
   if (EPI == 0 && p.res) {
@@ -819,14 +904,15 @@ int launch(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, c
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
   cudaError_t le = b200_launch_pdl(conv_tc_kernel<BN, EPI, HALO, DS>, dim3(grid), dim3(TC_THREADS + (HALO ? 32 : 0)),
-                                   (size_t)TcSmem<BN, HALO, DS>::TOTAL, st, a1, a2, w, om, rm, p);
+                                   (size_t)TcSmem<BN, HALO, DS>::TOTAL, st, a1, a2, w, om, rm, xm ? xm->x1 : a1,
+                                   xm ? xm->x2 : a1, p);
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
 }
 
 template <int BN, bool HALO, bool DS = false, bool GNF = false>
 int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& w, const CUtensorMap& om,
-                const ConvTcParams& p, cudaStream_t st) {
+                const ConvTcParams& p, cudaStream_t st, const XMaps* xm = nullptr) {
   using SP = typename TcSmemSel<BN, HALO, DS, true>::type;
   static int attr_state[B200_MAX_DEVICES];
   auto kern = conv_tc_kernel<BN, 0, HALO, DS, true, GNF>;
@@ -846,7 +932,7 @@ int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap&
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, a1, a2, w, om, rm, p);
+  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, a1, a2, w, om, rm, xm ? xm->x1 : a1, xm ? xm->x2 : a1, p);
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
 }
@@ -964,7 +1050,8 @@ extern "C" int b200_conv2d_tc_gn_preferred(int C1, int C2, int B, int H, int W, 
 static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
                           const float* temb, int temb_stride, const void* res, float out_scale, void* out,
                           int out_mode, const float* sample_mul, float* stats, const float* gn_coef, int B, int H, int W,
-                          int Cout, int ksize, cudaStream_t st);
+                          int Cout, int ksize, cudaStream_t st, const void* xs1 = nullptr, int Cs1 = 0,
+                          const void* xs2 = nullptr, int Cs2 = 0);
 
 extern "C" int b200_conv2d_tc(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
                               const float* temb, int temb_stride, const void* res, float out_scale, void* out,
@@ -986,10 +1073,26 @@ extern "C" int b200_conv2d_tc_gn(const void* x1, int C1, const void* x2, int C2,
                         W, Cout, ksize, st);
 }
 
+// The second convolution of a residual block with its 1x1 shortcut folded in (models/layerspp.py:266-274):
+//     out = (conv3x3(h; W1) + conv1x1(cat(xs1, xs2); W2) + bias) * out_scale,      bias = b1 + b2,
+// one GEMM over K = 9 (C1 + C2) + Cs1 + Cs2: the shortcut's K blocks are loaded from the block input at the centre tap
+// and meet the stacked weight [W1 | W2] ([Cout][9 (C1 + C2) + Cs1 + Cs2], K contiguous).  `Conv_2`'s own launch, its
+// output and the residual read of `Conv_1` disappear.  gn_coef != NULL: h = silu(groupnorm(raw x1 / x2)) as in
+// b200_conv2d_tc_gn (the shortcut sources are never normalised).  3x3, stride 1, Cs1 % 64 == Cs2 % 64 == 0.
+extern "C" int b200_conv2d_tc_sc(const void* x1, int C1, const void* x2, int C2, const float* gn_coef, const void* xs1,
+                                 int Cs1, const void* xs2, int Cs2, const void* w, const float* bias, const float* temb,
+                                 int temb_stride, float out_scale, void* out, float* stats, int B, int H, int W, int Cout,
+                                 cudaStream_t st) {
+  if (!xs1 || Cs1 <= 0) return B200_ERR_ARG;
+  if (gn_coef && !b200_conv2d_tc_gn_supported(C1, C2, B, H, W, Cout, 3)) return B200_ERR_UNSUPPORTED;
+  return conv2d_tc_impl(x1, C1, x2, C2, w, bias, temb, temb_stride, nullptr, out_scale, out, 0, nullptr, stats, gn_coef,
+                        B, H, W, Cout, 3, st, xs1, Cs1, xs2, Cs2);
+}
+
 static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
                           const float* temb, int temb_stride, const void* res, float out_scale, void* out,
                           int out_mode, const float* sample_mul, float* stats, const float* gn_coef, int B, int H, int W,
-                          int Cout, int ksize, cudaStream_t st) {
+                          int Cout, int ksize, cudaStream_t st, const void* xs1, int Cs1, const void* xs2, int Cs2) {
   if (!x1 || !w || !out || (C2 > 0 && !x2)) return B200_ERR_ARG;
   if (!b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, ksize, 1, out_mode)) return B200_ERR_UNSUPPORTED;
   if ((out_mode == 1 && (temb || res)) || (out_mode == 2 && temb)) return B200_ERR_UNSUPPORTED;
@@ -1010,7 +1113,13 @@ static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const 
   p.out = (bf16*)out; p.out_nchw = (float*)out; p.sample_mul = sample_mul; p.cout_true = Cout;
   p.stats = out_mode == 0 ? stats : nullptr; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h;
   p.gn_coef = gn_coef;
-  const int Ktot = ksize * ksize * (C1 + C2);
+  p.C3 = Cs1; p.C4 = Cs2;
+  if (Cs1 < 0 || Cs2 < 0 || Cs1 % TC_BK || Cs2 % TC_BK || (Cs1 > 0 && !xs1) || (Cs2 > 0 && !xs2) || (Cs2 > 0 && Cs1 == 0))
+    return B200_ERR_ARG;
+  if ((Cs1 + Cs2) > 0 && (out_mode != 0 || ksize != 3)) return B200_ERR_UNSUPPORTED;
+  const int Ktot = ksize * ksize * (C1 + C2) + Cs1 + Cs2;
+  XMaps xm;
+  const XMaps* xmp = (Cs1 + Cs2) > 0 ? &xm : nullptr;
   CUtensorMap a1, a2, wm;
   int rc = act_map(&a1, x1, B, H, W, C1, p.TW, p.TH, p.TB);
   if (rc) return rc;
@@ -1033,12 +1142,18 @@ static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const 
     else a2 = a1;
     rc = act_map(&om, out, B, H, W, Cout, HALO_TW, HALO_TH, 1);
     if (rc) return rc;
+    if (xmp) {
+      rc = act_map(&xm.x1, xs1, B, H, W, Cs1, HALO_TW, HALO_TH + 2, 1);
+      if (rc) return rc;
+      if (Cs2 > 0) { rc = act_map(&xm.x2, xs2, B, H, W, Cs2, HALO_TW, HALO_TH + 2, 1); if (rc) return rc; }
+      else xm.x2 = xm.x1;
+    }
     if (BN == 256) {
       CUtensorMap wh;                                     // each CTA of the pair loads 128 of the 256 weight rows
       rc = weight_map(&wh, w, Cout, Ktot, 128);
       if (rc) return rc;
-      if (gn_coef) return launch_pair<256, true, false, true>(a1, a2, wh, om, p, st);
-      return launch_pair<256, true>(a1, a2, wh, om, p, st);
+      if (gn_coef) return launch_pair<256, true, false, true>(a1, a2, wh, om, p, st, xmp);
+      return launch_pair<256, true>(a1, a2, wh, om, p, st, xmp);
     }
     if (halo_pair_enabled()) {
       CUtensorMap wh;                                     // each CTA of the pair loads 64 of the 128 weight rows
@@ -1047,25 +1162,31 @@ static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const 
       // B200_CONV_HALO_PAIR_DS=1: second staging buffer instead of the third weight-ring stage for convs with a
       // residual (measured: 128->128 0.304 -> 0.299 ms, 256->128 0.505 -> 0.529 ms; off)
       static const bool hp_ds = [] { const char* e = getenv("B200_CONV_HALO_PAIR_DS"); return e && e[0] == '1'; }();
-      if (gn_coef) return launch_pair<128, true, false, true>(a1, a2, wh, om, p, st);
-      if (res && hp_ds) return launch_pair<128, true, true>(a1, a2, wh, om, p, st);
-      return launch_pair<128, true>(a1, a2, wh, om, p, st);
+      if (gn_coef) return launch_pair<128, true, false, true>(a1, a2, wh, om, p, st, xmp);
+      if (res && hp_ds) return launch_pair<128, true, true>(a1, a2, wh, om, p, st, xmp);
+      return launch_pair<128, true>(a1, a2, wh, om, p, st, xmp);
     }
     if (gn_coef) return B200_ERR_UNSUPPORTED;
-    return launch<128, 0, true>(a1, a2, wm, om, p, st);
+    return launch<128, 0, true>(a1, a2, wm, om, p, st, xmp);
   }
   if (gn_coef) return B200_ERR_UNSUPPORTED;
   rc = act_map(&om, out, B, H, W, Cout, p.TW, p.TH, p.TB);
   if (rc) return rc;
+  if (xmp) {
+    rc = act_map(&xm.x1, xs1, B, H, W, Cs1, p.TW, p.TH, p.TB);
+    if (rc) return rc;
+    if (Cs2 > 0) { rc = act_map(&xm.x2, xs2, B, H, W, Cs2, p.TW, p.TH, p.TB); if (rc) return rc; }
+    else xm.x2 = xm.x1;
+  }
   if (ksize == 3 && BN == 256 && pair_enabled()) {
     CUtensorMap wh;                                       // each CTA of the pair loads 128 of the 256 weight rows
     rc = weight_map(&wh, w, Cout, Ktot, 128);
     if (rc) return rc;
-    return launch_pair<256, false>(a1, a2, wh, om, p, st);
+    return launch_pair<256, false>(a1, a2, wh, om, p, st, xmp);
   }
   if (ksize == 1 && ds_enabled())     // epilogue-bound: double-buffered staging
     return BN == 256 ? launch<256, 0, false, true>(a1, a2, wm, om, p, st) : launch<128, 0, false, true>(a1, a2, wm, om, p, st);
-  return BN == 256 ? launch<256, 0>(a1, a2, wm, om, p, st) : launch<128, 0>(a1, a2, wm, om, p, st);
+  return BN == 256 ? launch<256, 0>(a1, a2, wm, om, p, st, xmp) : launch<128, 0>(a1, a2, wm, om, p, st, xmp);
 }
 
 // 3x3 stride-2 VALID convolution (zero fill beyond the input extent) on the same kernel: the TMA box walks the input
@@ -1092,7 +1213,7 @@ extern "C" int b200_conv2d_tc_s2(const void* x, int C, const void* w, const floa
   p.num_n = Cout / BN;
   p.bias = bias; p.temb = nullptr; p.temb_stride = 0; p.res = (const bf16*)res; p.out_scale = out_scale;
   p.out = (bf16*)out; p.out_nchw = nullptr; p.sample_mul = nullptr; p.cout_true = Cout; p.narrow = 0;
-  p.stats = stats; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h; p.gn_coef = nullptr;
+  p.stats = stats; p.stat_slots = p.TB > 1 ? 1 : 2 * p.tiles_w * p.tiles_h; p.gn_coef = nullptr; p.C3 = 0; p.C4 = 0;
   CUtensorMap a1, wm, om;
   int rc = act_map(&a1, x, B, Hin, Win, C, p.TW, p.TH, p.TB, 2);
   if (rc) return rc;

@@ -168,8 +168,7 @@ class Net:
         h2 = self.gn_act(h1, p + ".GroupNorm_1", out_ch)
         scale = INV_SQRT2 if skip_rescale else 1.0
         if in_ch != out_ch or up or down:
-            skip = b.conv(xs, p + ".Conv_2", out_ch, 1, x2=xs2)
-            return b.conv(h2, p + ".Conv_1", out_ch, 3, res=skip, out_scale=scale, init_scale=init_scale)
+            return b.conv_sc(h2, p + ".Conv_1", p + ".Conv_2", xs, xs2, out_ch, scale, init_scale)
         if x2 is not None:
             raise NotImplementedError("identity skip over a concatenated input")
         return b.conv(h2, p + ".Conv_1", out_ch, 3, res=x, out_scale=scale, init_scale=init_scale)
@@ -189,9 +188,8 @@ class Net:
         if in_ch != out_ch:
             if conv_shortcut:
                 skip = b.conv(x, p + ".Conv_2", out_ch, 3, x2=x2)
-            else:
-                skip = b.conv(x, p + ".NIN_0", out_ch, 1, x2=x2, nin=True, init_scale=0.1)
-            return b.conv(h2, p + ".Conv_1", out_ch, 3, res=skip, out_scale=scale, init_scale=init_scale)
+                return b.conv(h2, p + ".Conv_1", out_ch, 3, res=skip, out_scale=scale, init_scale=init_scale)
+            return b.conv_sc(h2, p + ".Conv_1", p + ".NIN_0", x, x2, out_ch, scale, init_scale, nin2=True, nin2_init=0.1)
         if x2 is not None:
             raise NotImplementedError("identity skip over a concatenated input")
         return b.conv(h2, p + ".Conv_1", out_ch, 3, res=x, out_scale=scale, init_scale=init_scale)

@@ -327,6 +327,43 @@ class Builder:
         self.e.emit_conv(self, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, stride, pad, key)
         return out
 
+    def conv_sc(self, h, key1, key2, xs, xs2, cout, out_scale, init_scale, nin2=False, nin2_init=1.0):
+        """Second convolution of a residual block: (conv3x3(h; key1) + shortcut1x1(cat(xs, xs2); key2)) * out_scale
+        (models/layerspp.py:266-274, models/layers.py:648-655).  On the tensor-core path the shortcut rides Conv_1's K
+        loop (b200_conv2d_tc_sc: one launch, no skip tensor); otherwise two convolutions, the second adding the first."""
+        from . import tc
+        fusable = (not self.dry and self.e.use_tc and self.tape is None and tc.ENABLED and tc.FUSE_SHORTCUT
+                   and self.e.fuse_shortcut and (xs.H, xs.W) == (h.H, h.W) and xs.C % 64 == 0
+                   and (xs2 is None or xs2.C % 64 == 0) and xs.Ct == xs.C and (xs2 is None or xs2.Ct == xs2.C))
+        if fusable:
+            probe = self.new(h.H, h.W, cout)
+            fusable = tc.conv_supported(self, h, None, probe, 3, 1, (1, 1))
+        if not fusable:
+            skip = self.conv(xs, key2, cout, 1, x2=xs2, nin=nin2, init_scale=nin2_init)
+            return self.conv(h, key1, cout, 3, res=skip, out_scale=out_scale, init_scale=init_scale)
+        cx = xs.C + (xs2.C if xs2 is not None else 0)
+        if nin2:                                    # same registration order as the two-launch form above
+            self.param(key2 + ".W", (cx, cout), ("default", nin2_init))
+            self.param(key2 + ".b", (cout,), "zeros")
+        else:
+            self.param(key2 + ".weight", (cout, cx, 1, 1), ("default", nin2_init))
+            self.param(key2 + ".bias", (cout,), "zeros")
+        self.param(key1 + ".weight", (cout, h.Ct, 3, 3), ("default", init_scale))
+        self.param(key1 + ".bias", (cout,), "zeros")
+        out = self.new(h.H, h.W, cout)
+        w, bias = self.e.packed_conv_sc(key1, key2, nin2, h.C, cx, cout)
+        flops = 2 * self.B * h.H * h.W * cout * (9 * h.Ct + cx)
+        gn = None
+        if isinstance(h, LazyGN) and h.real is None and tc.conv_gn_supported(self, h.src1, h.src2, out, 3, 1, (1, 1)):
+            gn = h
+        x = None if gn is not None else (self.materialize(h) if isinstance(h, LazyGN) else h)
+        tc.emit_conv_sc(self, x, gn, xs, xs2, w, bias, None, out_scale, out, flops)
+        self.e.tc_convs += 1
+        self.e.sc_fused += 1
+        if gn is not None:
+            self.e.gn_fused += 1
+        return out
+
     def upfirdn(self, x, up, down, pad):
         Ho = (x.H * up + pad[0] + pad[1] - 4) // down + 1
         Wo = (x.W * up + pad[0] + pad[1] - 4) // down + 1
@@ -390,6 +427,9 @@ class ScoreEngine:
         # (B200_FUSE_GN=0 / all: A/B measurements)
         self.fuse_gn_conv = {"0": False, "all": "all"}.get(os.environ.get("B200_FUSE_GN", "1"), True)
         self.gn_fused = 0
+        # the 1x1 shortcut of a residual block folded into its second conv's K loop (B200_FUSE_SC=0: A/B measurements)
+        self.fuse_shortcut = os.environ.get("B200_FUSE_SC", "1") != "0"
+        self.sc_fused = 0
         self.workspace = Workspace(self.device)
         self.params = {}           # reference-layout fp32 tensors on device
         self._packed = {}
@@ -480,6 +520,22 @@ class ScoreEngine:
             p = torch.zeros(cout_store, kh, kw, cin_store, device=self.device, dtype=torch.float32)
             p[:cout, :, :, :cin] = w.permute(0, 2, 3, 1)
             self._packed[pk] = p.to(_TORCH_DT[self.dt]).contiguous()
+        return self._packed[pk]
+
+    def packed_conv_sc(self, key1, key2, nin2, cin, cx, cout):
+        """[W1 | W2]: [Cout][9 cin + cx] in the activation dtype (K contiguous) and the summed bias b1 + b2 (fp32)."""
+        pk = (key1, key2, "sc")
+        if pk not in self._packed:
+            w1 = self.params[key1 + ".weight"]                                   # [Cout, Cin, 3, 3]
+            if nin2:
+                w2 = self.params[key2 + ".W"].t().contiguous()                   # [Cout, Cx]
+                b2 = self.params[key2 + ".b"]
+            else:
+                w2 = self.params[key2 + ".weight"].reshape(cout, -1)             # [Cout, Cx, 1, 1] -> [Cout, Cx]
+                b2 = self.params[key2 + ".bias"]
+            assert w1.shape == (cout, cin, 3, 3) and w2.shape == (cout, cx), (w1.shape, w2.shape)
+            w = torch.cat([w1.permute(0, 2, 3, 1).reshape(cout, 9 * cin), w2], 1)
+            self._packed[pk] = (w.to(_TORCH_DT[self.dt]).contiguous(), (self.params[key1 + ".bias"] + b2).contiguous())
         return self._packed[pk]
 
     def packed_bias(self, key, nin, cout_store):

@@ -22,7 +22,11 @@ _lib.register_signature("b200_conv2d_tc_gn_preferred", [c_int] * 7)
 _lib.register_signature("b200_conv2d_tc_gn", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float,
                                               c_vp, c_vp, c_int, c_int, c_int, c_int, c_int])
 
+_lib.register_signature("b200_conv2d_tc_sc", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp,
+                                              c_int, c_float, c_vp, c_vp, c_int, c_int, c_int, c_int])
+
 ENABLED = True
+FUSE_SHORTCUT = True  # Conv_2 (1x1 shortcut) folded into Conv_1's K loop (b200_conv2d_tc_sc)
 FUSE_GN = True        # GroupNorm + SiLU inside the consumer conv's operand pipeline (b200_conv2d_tc_gn)
 
 
@@ -64,6 +68,27 @@ def emit_conv_gn(b, gn, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
            b.temb_stride, res, out_scale, out, None, b.B, x1.H, x1.W, out.C, ksize, flops=flops,
            tag="%dx%d %dx%d %d->%d gn" % (ksize, ksize, x1.H, x1.W, x1.C + c2, out.C))
     out.producer = (len(b.plan.ops) - 1, 12)      # position of the `stats` argument
+
+
+def emit_conv_sc(b, x, gn, xs1, xs2, w, bias, temb_ptr, out_scale, out, flops):
+    """Conv_1 + folded 1x1 shortcut.  `x`: the (materialised) conv input, or None when `gn` (a LazyGN) is fused in."""
+    coef = None
+    if gn is not None:
+        x1, x2 = gn.src1, gn.src2
+        s1, t1 = request_stats(b, x1)
+        s2, t2 = request_stats(b, x2) if x2 is not None else (None, 0)
+        coef_t = b.f32(b.B * gn.C * 2)
+        b.emit("b200_gn_coef", s1, t1, x1.C, s2, t2, x2.C if x2 is not None else 0, b.B, x1.H * x1.W, gn.groups,
+               b.e.dev(gn.key + ".weight"), b.e.dev(gn.key + ".bias"), 1e-6, coef_t.data_ptr())
+        coef = coef_t.data_ptr()
+    else:
+        x1, x2 = x, None
+    p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+    q2, d2 = (xs2, xs2.C) if xs2 is not None else (None, 0)
+    b.emit("b200_conv2d_tc_sc", x1, x1.C, p2, c2, coef, xs1, xs1.C, q2, d2, w.data_ptr(), bias.data_ptr(), temb_ptr,
+           b.temb_stride, out_scale, out, None, b.B, x1.H, x1.W, out.C, flops=flops,
+           tag="3x3 %dx%d %d->%d +sc %d%s" % (x1.H, x1.W, x1.C + c2, out.C, xs1.C + d2, " gn" if gn is not None else ""))
+    out.producer = (len(b.plan.ops) - 1, 15)      # position of the `stats` argument
 
 
 def head_supported(b, x, cout, ksize):

@@ -164,6 +164,14 @@ int b200_conv2d_tc_stat_slots(int B, int H, int W);
 int b200_gn_coef(const float* st1, int T1, int C1, const float* st2, int T2, int C2, int B, int HW, int G,
                  const float* gamma, const float* beta, float eps, float* coef, cudaStream_t stream);
 int b200_conv2d_tc_gn_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize);
+/* Conv_1 of a residual block with its 1x1 shortcut `Conv_2(x)` folded in (models/layerspp.py:266-274):
+ * out = (conv3x3(h; W1) + conv1x1(cat(xs1, xs2); W2) + bias) * out_scale with bias = b1 + b2 and
+ * w = [Cout][9 (C1 + C2) + Cs1 + Cs2] = [W1 | W2]; the shortcut's K blocks ride the same K loop at the centre tap, so
+ * Conv_2's launch, its output tensor and Conv_1's residual read disappear.  gn_coef (may be NULL) as b200_conv2d_tc_gn.
+ * Shapes: whatever b200_conv2d_tc_supported(C1, C2, B, H, W, Cout, 3, 1, 0) takes, Cs1 % 64 == Cs2 % 64 == 0. */
+int b200_conv2d_tc_sc(const void* x1, int C1, const void* x2, int C2, const float* gn_coef, const void* xs1, int Cs1,
+                      const void* xs2, int Cs2, const void* w, const float* bias, const float* temb, int temb_stride,
+                      float out_scale, void* out, float* stats, int B, int H, int W, int Cout, cudaStream_t stream);
 /* 1 where the fused form is also the FASTER one (256-wide tiles; the 128-wide ones are shared-memory-bandwidth bound
  * and lose to conv + standalone GroupNorm): what the engine's planner asks */
 int b200_conv2d_tc_gn_preferred(int C1, int C2, int B, int H, int W, int Cout, int ksize);

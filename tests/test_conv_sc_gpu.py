@@ -1,0 +1,107 @@
+"""b200_conv2d_tc_sc: the second convolution of a residual block with its 1x1 shortcut folded into the K loop
+(csrc/conv_tc.cu, `kb_extra` K blocks at the centre tap) against a plain PyTorch fp32 reference of
+`(conv3x3(h) + conv1x1(cat(xs1, xs2)) + b1 + b2) * scale` (models/layerspp.py:266-274) on the same bf16-rounded operands,
+through every tile variant the engine selects; then the whole C3 network with and without the folding."""
+import pytest
+import torch
+
+import cases
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [  # B, H, W, C1 (conv input), Cs1, Cs2 (shortcut sources), Cout, gn-fused input
+    (3, 32, 32, 128, 256, 128, 128, False),    # halo + pair, 128-wide, two shortcut sources (up path 384 -> 128)
+    (2, 32, 32, 128, 128, 128, 128, True),     # ... with GroupNorm fused into the 3x3 operand (shortcut stays raw)
+    (160, 16, 16, 256, 256, 256, 256, False),  # halo + pair, 256-wide, persistent loop over many tiles
+    (160, 16, 16, 256, 128, 0, 256, True),     # ... GroupNorm-fused, one source (down path 128 -> 256)
+    (297, 8, 8, 256, 256, 256, 256, False),    # batch-spanning tiles, CTA pair, odd tile count
+    (9, 4, 4, 256, 256, 256, 256, False),      # 8-image tiles, ragged batch, single-CTA 128-wide tiles
+    (5, 8, 8, 256, 256, 0, 256, False),        # down block: same width, FIR-resampled shortcut source
+    (2, 64, 64, 128, 256, 128, 128, False),    # 64 x 64 level (DDPM NIN shortcut 384 -> 128)
+]
+
+
+def _stats_of(x):
+    B, H, W, C = x.shape
+    f = x.float().reshape(B, H * W, C)
+    return torch.stack([f.sum(1), (f * f).sum(1)], -1).reshape(B, 1, C, 2).contiguous()
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+def test_conv_with_folded_shortcut_matches_torch_fp32(cuda, shape):
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import engine, tc  # noqa: F401
+    B, H, W, C1, Cs1, Cs2, Cout, gn = shape
+    lib = _lib.lib()
+    g = torch.Generator(device="cpu").manual_seed(sum(shape[:7]))
+    rn = lambda *s: torch.randn(*s, generator=g)
+    x = (rn(B, H, W, C1) * (0.5 + rn(C1).abs()) + (rn(C1) if gn else 0)).to(cuda, torch.bfloat16)
+    xs1 = rn(B, H, W, Cs1).to(cuda, torch.bfloat16)
+    xs2 = rn(B, H, W, Cs2).to(cuda, torch.bfloat16) if Cs2 else None
+    Cx = Cs1 + Cs2
+    w1 = (rn(Cout, 3, 3, C1) / (9 * C1) ** 0.5).to(cuda, torch.bfloat16)
+    w2 = (rn(Cout, Cx) / Cx ** 0.5).to(cuda, torch.bfloat16)
+    w = torch.cat([w1.reshape(Cout, 9 * C1), w2], 1).contiguous()
+    bias = rn(Cout).to(cuda)
+    temb = rn(B, Cout).to(cuda)
+    scale = 0.70710678
+    coef, h = None, x
+    if gn:
+        assert lib.b200_conv2d_tc_gn_supported(C1, 0, B, H, W, Cout, 3) == 1
+        G = min(C1 // 4, 32)
+        gamma, beta = (1 + 0.2 * rn(C1)).to(cuda), (0.3 * rn(C1)).to(cuda)
+        st = _stats_of(x)
+        coef = torch.empty(B, C1, 2, device=cuda)
+        _lib.check(lib.b200_gn_coef(_lib.ptr(st), 1, C1, None, 0, 0, B, H * W, G, _lib.ptr(gamma), _lib.ptr(beta), 1e-6,
+                                    _lib.ptr(coef), _lib.stream()), "b200_gn_coef")
+        hn = torch.nn.functional.group_norm(x.float().permute(0, 3, 1, 2), G, gamma, beta, eps=1e-6)
+        h = torch.nn.functional.silu(hn).permute(0, 2, 3, 1).to(torch.bfloat16)
+    T = lib.b200_conv2d_tc_stat_slots(B, H, W)
+    out = torch.full((B, H, W, Cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+    stats = torch.full((B, T, Cout, 2), float("nan"), device=cuda)
+    rc = lib.b200_conv2d_tc_sc(_lib.ptr(x), C1, None, 0, _lib.ptr(coef), _lib.ptr(xs1), Cs1, _lib.ptr(xs2), Cs2,
+                               _lib.ptr(w), _lib.ptr(bias), _lib.ptr(temb), Cout, scale, _lib.ptr(out), _lib.ptr(stats),
+                               B, H, W, Cout, _lib.stream())
+    _lib.check(rc, "b200_conv2d_tc_sc")
+    torch.cuda.synchronize()
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref = torch.nn.functional.conv2d(h.float().permute(0, 3, 1, 2), w1.float().permute(0, 3, 1, 2), padding=1)
+    xx = torch.cat([xs1, xs2], -1) if Cs2 else xs1
+    ref = ref.permute(0, 2, 3, 1) + xx.float() @ w2.float().t()
+    ref = (ref + bias + temb[:, None, None, :]) * scale
+    o = out.float()
+    assert torch.isfinite(o).all()
+    err, mag = (o - ref).abs().max().item(), ref.abs().max().item()
+    assert err <= 2 ** -7 * mag, (err, mag)
+    rel = ((o - ref).norm() / ref.norm()).item()
+    assert rel < (6e-3 if gn else 4e-3), rel
+    sd = stats.double().sum(1)
+    od = out.double().reshape(B, H * W, Cout)
+    assert torch.allclose(sd[..., 0], od.sum(1), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(sd[..., 1], (od * od).sum(1), rtol=1e-4, atol=1e-2)
+
+
+@pytest.mark.parametrize("name,B", [("cifar10_ncsnpp_ve", 2), ("cifar10_ncsnpp_ve", 40), ("nc_ddpm_vp", 1)])
+def test_network_with_folded_shortcuts(cuda, name, B):
+    """Whole network: folded plan vs two-launch plan (they differ only by the bf16 rounding of the skip tensor, which
+    the folded form no longer performs) and vs the reference's golden output."""
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    cfg, sd, x, labels, out = cases.score_case(name)
+    g = torch.Generator().manual_seed(B)
+    S, C = cfg.data.image_size, cfg.data.num_channels
+    xb = (torch.rand(B, C, S, S, generator=g) * 1.5 - 0.25).to(cuda)
+    lb = labels[:1].repeat(B).to(cuda) if name != "cifar10_ncsnpp_ve" else torch.exp(torch.rand(B, generator=g) * 8.5 - 4.6).to(cuda)
+    outs, counts = [], []
+    for fold in (False, True):
+        m = mutils.ScoreModel(cfg, device=cuda, precision="bf16", init=False)
+        m.load_state_dict(sd)
+        m.engine.fuse_shortcut = fold
+        outs.append(m(xb, lb))
+        names = [n for _, _, n in m.engine.plan(B).ops]
+        counts.append((len(names), names.count("b200_conv2d_tc_sc")))
+        if fold and B == x.shape[0]:
+            assert cases.rel_l2(m(x.to(cuda), labels.to(cuda)).cpu(), out) < 2e-2
+    (n0, f0), (n1, f1) = counts
+    assert f0 == 0 and f1 >= 10 and n1 == n0 - f1, counts          # every folded shortcut removed one launch
+    assert cases.rel_l2(outs[1].cpu(), outs[0].cpu()) < 8e-3, cases.rel_l2(outs[1].cpu(), outs[0].cpu())
