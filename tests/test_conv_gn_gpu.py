@@ -119,7 +119,8 @@ def test_network_with_and_without_gn_fusion_is_bit_identical(cuda, B):
         m.engine.fuse_gn_conv = fuse
         outs.append(m(xb, lb))
         names = [n for _, _, n in m.engine.plan(B).ops]
-        counts.append((sum(n.startswith("b200_gn_apply") for n in names), names.count("b200_conv2d_tc_gn")))
+        # one b200_gn_coef launch per GroupNorm-fused convolution (b200_conv2d_tc_gn, or b200_conv2d_tc_sc with gn_coef)
+        counts.append((sum(n.startswith("b200_gn_apply") for n in names), names.count("b200_gn_coef")))
     assert torch.equal(outs[0], outs[1]), (outs[0] - outs[1]).abs().max().item()
     (gn0, f0), (gn1, f1) = counts
     assert f0 == 0 and f1 >= 30, counts
