@@ -45,6 +45,8 @@ _SIGNATURES = {
     "b200_sde_update": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_float, c_int, c_ll,
                         c_u64, c_u64, c_ll, c_vp],
     "b200_fill_normal": [c_vp, c_ll, c_float, c_u64, c_u64, c_ll, c_vp],
+    "b200_mask_mix": [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.POINTER(c_float), ctypes.POINTER(c_float),
+                      c_int, c_int, c_ll, c_u64, c_u64, c_ll, c_vp],
     "b200_step_advance": [c_vp, c_int, c_vp],
     "b200_grid_sample_fwd": [c_int, c_vp, c_vp, c_vp] + [c_int] * 10 + [c_vp],
     "b200_grid_sample_bwd": [c_int, c_vp, c_vp, c_vp, c_vp, c_vp] + [c_int] * 10 + [c_vp],

@@ -1,8 +1,11 @@
 """Inpainting and colorisation with PC samplers, reference signatures (controllable_generation.py:8-180).
 
-The predictor / corrector updates are the engine-backed ones of `sampling` (fused kernels); after every update the known
-part of the image is replaced by freshly noised data, `x (1 - m) + (mean_t(data) + std_t z) m`
-(controllable_generation.py:44-54, 132-141).  Noise comes through `sampling._noise` so that tests can inject it."""
+After every predictor / corrector update the known part of the image is replaced by freshly noised data,
+`x (1 - m) + (mean_t(data) + std_t z) m` (controllable_generation.py:44-54, 132-141).  With a B200 score model and the
+built-in predictor / corrector classes the whole thing runs inside `sampling.FusedPCLoop`: the mix is one fused kernel
+(`b200_mask_mix`, colour-basis change included) in the step's launch sequence, the schedule lives in device tables and
+the step replays as a CUDA graph.  User-registered classes take the generic loop below (their `update_fn` + the same
+arithmetic in torch).  Noise comes through `sampling._noise` so that tests can inject it."""
 import functools
 
 import torch
@@ -22,6 +25,15 @@ def _prior(sde, shape, device):
         return sde.prior_sampling(shape).to(device)
     from . import sde_lib
     return z * (sde.sigma_max if isinstance(sde, sde_lib.VESDE) else 1.0)
+
+
+def _fused(model, sde, predictor, corrector, snr, n_steps, probability_flow, continuous, eps, denoise, x0, mix):
+    loop = sampling.FusedPCLoop(model, sde, tuple(x0.shape), predictor, corrector, snr, n_steps, probability_flow,
+                                continuous, eps, mix=mix)
+    with torch.cuda.device(loop.dev):
+        loop.reset(x0.to(loop.dev))
+        loop.run(sde.N)
+        return (loop.x_mean if denoise else loop.x).clone()
 
 
 def _update_fns(sde, predictor, corrector, snr, n_steps, probability_flow, continuous):
@@ -56,6 +68,9 @@ def get_pc_inpainter(sde, predictor, corrector, inverse_scaler, snr, n_steps=1, 
     def pc_inpainter(model, data, mask):
         with torch.no_grad():
             x = data * mask + _prior(sde, data.shape, data.device) * (1. - mask)
+            if sampling.is_fusable(model, sde, predictor, corrector) and data.dim() == 4 and data.shape[1] <= 4:
+                return inverse_scaler(_fused(model, sde, predictor, corrector, snr, n_steps, probability_flow, continuous,
+                                             eps, denoise, x, dict(data=data, mask=mask)))
             timesteps = torch.linspace(sde.T, eps, sde.N)
             for i in range(sde.N):
                 t = timesteps[i]
@@ -108,6 +123,9 @@ def get_pc_colorizer(sde, predictor, corrector, inverse_scaler, snr, n_steps=1, 
             mask = get_mask(gray_scale_img)
             x = couple(decouple(gray_scale_img) * mask
                        + decouple(_prior(sde, shape, gray_scale_img.device) * (1. - mask)))
+            if sampling.is_fusable(model, sde, predictor, corrector) and len(shape) == 4 and shape[1] == 3:
+                return inverse_scaler(_fused(model, sde, predictor, corrector, snr, n_steps, probability_flow, continuous,
+                                             eps, denoise, x, dict(data=gray_scale_img, mask=mask, M=M, Minv=invM)))
             timesteps = torch.linspace(sde.T, eps, sde.N)
             for i in range(sde.N):
                 t = timesteps[i]

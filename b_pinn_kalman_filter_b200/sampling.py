@@ -403,7 +403,10 @@ class FusedPCLoop:
     (n_steps Langevin/ALD updates) + predictor, i.e. (n_steps + 1) score-network forwards."""
 
     def __init__(self, model, sde, shape, predictor, corrector, snr, n_steps, probability_flow, continuous, eps,
-                 process_group=None, rank_offset=0, total_batch=None, use_graph=True, seed=None):
+                 process_group=None, rank_offset=0, total_batch=None, use_graph=True, seed=None, mix=None):
+        """mix: controllable generation (controllable_generation.py:44-54, 132-141) -- dict(data, mask[, M, Minv]); after
+        the corrector and after the predictor of every step the known part of the state is replaced by freshly noised
+        data (b200_mask_mix), inside the same launch sequence / CUDA graph."""
         eng = model.engine
         self.eng = eng
         self.sde = sde
@@ -476,6 +479,16 @@ class FusedPCLoop:
         self.sums = torch.zeros(2, device=dev, dtype=torch.float32)
         self.scaled = torch.zeros_like(self.x) if (self.corr and self.corr[0] == "langevin" and
                                                    not bool((mult == 1).all())) else None
+        self.mix = None
+        if mix is not None:
+            import ctypes
+            if len(self.shape) != 4 or self.shape[1] > 4:
+                raise NotImplementedError("fused mask-mix handles [B, C <= 4, H, W] states")
+            a_t, s_t = sde.marginal_coef(t)
+            f32 = lambda v: v.detach().to(device=dev, dtype=torch.float32).expand(self.shape).contiguous()
+            arr = lambda m: None if m is None else (ctypes.c_float * 9)(*[float(v) for v in m.reshape(-1).tolist()])
+            self.mix = dict(data=f32(mix["data"]), mask=f32(mix["mask"]), M=arr(mix.get("M")), Minv=arr(mix.get("Minv")),
+                            a=a_t.to(torch.float32).expand_as(t).contiguous(), s=s_t.to(torch.float32).contiguous())
         self.graph = None
         self.offset_base = reserve_streams(STREAMS_PER_STEP * (N + 1))
         self.launches_per_step = 0
@@ -532,6 +545,15 @@ class FusedPCLoop:
                    "b200_sde_update")
         return n + 1
 
+    def _mix(self, st, off):
+        m = self.mix
+        z = _noise(self.shape, self.dev)
+        _lib.check(self.lib.b200_mask_mix(_lib.ptr(self.x), _lib.ptr(self.x_mean), _lib.ptr(m["data"]), _lib.ptr(m["mask"]),
+                                          _lib.ptr(z), _lib.ptr(m["a"]), _lib.ptr(m["s"]), _lib.ptr(self.step_dev), m["M"],
+                                          m["Minv"], self.B, self.shape[1], self.shape[2] * self.shape[3], self.seed, off,
+                                          self.elem_base, st), "b200_mask_mix")
+        return 1
+
     def _step_body(self, st):
         """All launches of one PC step.  Noise streams: update k of device step i draws Philox stream
         base + i * 16 + k (the kernels add the device step counter themselves), so the launch arguments are the
@@ -542,8 +564,14 @@ class FusedPCLoop:
             for _ in range(self.n_steps):
                 n += self._corrector(st, self.offset_base + k)
                 k += 1
+        if self.mix:            # the reference mixes after the corrector AND after the predictor, `none` ones included
+            n += self._mix(st, self.offset_base + k)
+            k += 1
         if self.pred:
             n += self._predictor(st, self.offset_base + k)
+            k += 1
+        if self.mix:
+            n += self._mix(st, self.offset_base + k)
         _lib.check(self.lib.b200_step_advance(_lib.ptr(self.step_dev), 1, st), "b200_step_advance")
         return n + 1
 
@@ -581,7 +609,7 @@ class FusedPCLoop:
     def _graphable(self):
         needs_nccl = self.world > 1 and self.corr is not None and self.corr[0] == "langevin" and self.xchg is None
         return (self.use_graph and NOISE_FN is None and not needs_nccl and self.scaled is None
-                and self.n_steps + 1 <= 16)
+                and self.n_steps + 3 <= STREAMS_PER_STEP)
 
     def run(self, n_iters):
         """n_iters PC steps.  After one eager step (lazy initialisation of kernels / TMA descriptors) the step is
@@ -605,6 +633,15 @@ class FusedPCLoop:
         self._used = True
         self.step_host += n_iters
         return (n_iters + 1) * self.launches_per_step
+
+
+def is_fusable(model, sde, predictor, corrector):
+    """The fused device loop takes B200 score models with the BUILT-IN predictor / corrector classes; user-registered
+    subclasses go through the generic loop that calls their `update_fn`."""
+    return (isinstance(model, mutils.ScoreModel)
+            and (predictor is None or predictor in _BUILTIN_PREDICTORS)
+            and (corrector is None or corrector in _BUILTIN_CORRECTORS)
+            and isinstance(sde, (sde_lib.VPSDE, sde_lib.subVPSDE, sde_lib.VESDE)))
 
 
 def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
@@ -633,10 +670,7 @@ def get_pc_sampler(sde, shape, predictor, corrector, inverse_scaler, snr,
                                             continuous=continuous, snr=snr, n_steps=n_steps)
 
     def fusable(model):
-        return (isinstance(model, mutils.ScoreModel)
-                and (predictor is None or predictor in _BUILTIN_PREDICTORS)
-                and (corrector is None or corrector in _BUILTIN_CORRECTORS)
-                and isinstance(sde, (sde_lib.VPSDE, sde_lib.subVPSDE, sde_lib.VESDE)))
+        return is_fusable(model, sde, predictor, corrector)
 
     if prior not in ('auto', 'host', 'device'):
         raise ValueError("get_pc_sampler: prior must be 'auto', 'host' or 'device' (got %r)" % (prior,))

@@ -240,8 +240,64 @@ def aux_measurements(dev, pk):
     out["ns_step"] = {"shape": "B=256 192x192 fp32, velocity+pressure+density", "ms_per_step": ms,
                       "cell_updates_per_s": cells / ms * 1e3, "achieved": 52 * cells / ms / 1e6, "peak": pk["hbm"],
                       "unit": "GB/s", "frac": 52 * cells / ms / 1e6 / pk["hbm"],
-                      "algorithmic_bytes_per_cell": 52}
+                      "algorithmic_bytes_per_cell": 52,
+                      "achieved_at_32B_per_cell": 32 * cells / ms / 1e6, "frac_at_32B_per_cell": 32 * cells / ms / 1e6 / pk["hbm"],
+                      "bound": "fp32 instruction issue, not HBM: ~490 SASS instructions per cell per step (cuobjdump: "
+                               "ns_velocity4 ~250, ns_cip4 160, ns_pressure4 82; 57 of the 160 are FP math) = >= 130 us at 4 "
+                               "warp-instructions/clk/SM for 9.44 M cells"}
+    # the kernel to beat: the reference's own extension (oracle/_ref, op/ns_step_kernel.cu rebuilt for sm_100) at the same
+    # shape -- its update_velocity is only CORRECT at B = 1; timed anyway, it moves the same bytes
+    try:
+        from oracle import build_ref_ext
+        ext = build_ref_ext.load_ext("ns_step_forward")
+        if ext is None:
+            raise RuntimeError("oracle/_ref/ns_step_forward not built")
+
+        def ref_step():
+            v = ext.update_velocity(vel, pres, dt, dx)
+            p = ext.update_pressure(pres, v, dt, dx)
+            ext.update_density(dens, v, dt, dx)
+            return p
+
+        rms = timeit(ref_step, iters=5)
+        out["ns_step"]["reference_extension"] = {"ms_per_step": rms, "speedup": rms / ms,
+                                                 "kernel": "op/ns_step_kernel.cu:96-234 + op/ns_step.cpp:45-102, 9 launches"}
+    except Exception as e:  # noqa: BLE001
+        out["ns_step"]["reference_extension"] = {"unavailable": repr(e)[:160]}
     del vel, pres, dens
+    # CPU legs of the side metrics: the C restatement of ns_step (-fopenmp, all host cores) on a bounded
+    # sample, and the reference's upfirdn2d_native arithmetic (F.pad + F.conv2d, op/upfirdn2d.py:159-200) at the C5 shape
+    try:
+        import numpy as np
+        from oracle import ns_step_ref
+        d0, v0, p0 = ns_step_ref.synthetic_fields(16, 192, seed=0)
+        ns_step_ref.update_velocity(v0, p0, dt, dx)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            v1 = ns_step_ref.update_velocity(v0, p0, dt, dx)
+            ns_step_ref.update_pressure(p0, v1, dt, dx)
+            ns_step_ref.update_density(d0, v1, dt, dx)
+        cs = (time.perf_counter() - t0) / 3
+        out["ns_step"]["cpu_baseline"] = {"value": 16 * 192 * 192 / cs, "unit": "cell updates/s", "cores": os.cpu_count(),
+                                          "kind": "port", "sample": "3 steps at B=16 192x192, oracle/ns_step_ref.c -fopenmp",
+                                          "gpu_over_cpu": (cells / ms * 1e3) / (16 * 192 * 192 / cs)}
+        import torch.nn.functional as F
+        torch.set_num_threads(os.cpu_count() or 1)
+        xc = torch.randn(128, 1, 256, 256)
+        kc = torch.outer(torch.tensor([1., 3., 3., 1.]), torch.tensor([1., 3., 3., 1.]))
+        kc = (kc / kc.sum()).flip(0, 1).view(1, 1, 4, 4)
+        fcpu = lambda: F.conv2d(F.pad(xc, [1, 1, 1, 1]), kc)[:, :, ::2, ::2]
+        fcpu()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            fcpu()
+        cs = (time.perf_counter() - t0) / 3
+        nbc = 4 * (xc.numel() + xc.numel() // 4)
+        out["upfirdn2d"]["cpu_baseline"] = {"value": nbc / cs / 1e9, "unit": "GB/s", "cores": os.cpu_count(), "kind": "port",
+                                            "sample": "down2 of 128 planes 256x256 (1/8 of the C5 shape), the arithmetic of "
+                                                      "upfirdn2d_native: pad + conv2d + decimate, torch CPU"}
+    except Exception as e:  # noqa: BLE001
+        out["cpu_legs_error"] = repr(e)[:160]
     out["other_configs"] = other_config_measurements(dev, timeit)
     return out
 

@@ -100,6 +100,13 @@ int b200_langevin_norm_sums_xchg(float* sums2, const float* ss_score, const floa
 int b200_langevin_norms_static_max_batch(void);
 int b200_langevin_norms_static(float* sums2, const float* score, const float* z, int B, long long n_per, uint64_t seed,
                                uint64_t offset, long long elem_base, const int* step, cudaStream_t stream);
+/* controllable generation (controllable_generation.py:44-54, 132-141): after a predictor / corrector update the known
+ * part of the state is replaced by freshly noised data, y = T^-1(T(x)(1-m) + (a T(data) + s z) m), y_mean likewise with
+ * the noise-free data term; T = identity (inpainting, M = Minv = NULL) or the 3x3 colour basis (colourisation, C == 3;
+ * M, Minv are HOST pointers to 9 floats).  [B,C,H,W] fp32, C <= 4; a (NULL = 1), s: [B] or per-step tables with `step`. */
+int b200_mask_mix(float* x, float* x_mean, const float* data, const float* mask, const float* z, const float* a,
+                  const float* s, const int* step, const float* M, const float* Minv, int B, int C, long long HW,
+                  uint64_t seed, uint64_t offset, long long elem_base, cudaStream_t stream);
 int b200_sde_update(float* x, float* x_mean, const float* score, const float* z, const float* a, const float* b,
                     const float* c, const int* step, int langevin, const float* norm_sums, float inv_batch_total,
                     float snr, int B, long long n_per, uint64_t seed, uint64_t offset, long long elem_base,
