@@ -322,6 +322,35 @@ def other_config_measurements(dev, timeit):
         ms = timeit(lambda: plan.run(_lib.stream()), iters=5)
         res[tag] = {"batch": B, "ms_per_forward": ms, "tflops": plan.flops() / ms / 1e9, "launches": len(plan.ops),
                     "samples_per_s_per_gpu": B / (ms * 1e-3 * fwd_per_sample), "finite": bool(torch.isfinite(y).all())}
+        # the same config END TO END through the public API (get_pc_sampler: host prior -> H2D, PC steps, samples -> D2H)
+        # over n_run steps of its N-step schedule; per-step cost is schedule-independent, so samples/s = B / (t / n_run * N)
+        from b_pinn_kalman_filter_b200 import sampling, sde_lib
+        n_run = 50
+        mm = cfg.model
+        if cfg.training.sde == "vesde":
+            sde_r, eps = sde_lib.VESDE(mm.sigma_min, mm.sigma_max, n_run), 1e-5
+        else:
+            sde_r, eps = sde_lib.VPSDE(mm.beta_min, mm.beta_max, n_run), 1e-3
+        shape = (B, C, S, S)
+        host_prior = torch.randn(shape).pin_memory()
+        sde_r.prior_sampling = lambda shp: host_prior
+        fn = sampling.get_pc_sampler(sde_r, shape, sampling.get_predictor(cfg.sampling.predictor),
+                                     sampling.get_corrector(cfg.sampling.corrector), lambda v: v, cfg.sampling.snr,
+                                     n_steps=cfg.sampling.n_steps_each, continuous=cfg.training.continuous, denoise=True,
+                                     eps=eps, device=dev)
+        fn(m)                                             # warm-up: plans, graph capture
+        host_out = torch.empty(shape).pin_memory()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        xs, nfe = fn(m)
+        host_out.copy_(xs)
+        torch.cuda.synchronize()
+        dt_run = time.perf_counter() - t0
+        res[tag]["e2e"] = {"api": "sampling.get_pc_sampler(%s + %s)(model), pinned-host prior -> H2D, %d of %d PC steps, "
+                                  "samples -> D2H" % (cfg.sampling.predictor, cfg.sampling.corrector, n_run, mm.num_scales),
+                           "seconds": dt_run, "ms_per_pc_step": dt_run / n_run * 1e3,
+                           "samples_per_s_per_gpu": B / (dt_run / n_run * mm.num_scales), "nfe": nfe,
+                           "finite": bool(torch.isfinite(host_out).all())}
         del m, plan
         torch.cuda.empty_cache()
     cfg = configs.get_config("inverse/nc_ddpmpp_inpaint_dps")
