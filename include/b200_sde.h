@@ -256,6 +256,36 @@ int b200_rk_stage(float* x32_out, double* y_out, const double* y, const float* K
 int b200_rk_error(double* partial, const double* y, const double* y_new, const float* K, long long kstride, int ns,
                   const double* e_host, double h, double atol, double rtol, long long n, cudaStream_t stream);
 
+/* ---- training step (losses.py:165-222 step_fn: loss.backward(); optimize_fn = warm-up + clip_grad_norm_ + Adam,
+ * losses.py:48-66; models/ema.py:36-56) -------------------------------------------------------------------------------
+ * Weight gradients are contracted by b200_conv2d_tc / b200_conv2d_simt over K = pixels: b200_transpose2d gives dY^T
+ * [Cout][P], b200_im2col_t the transposed im2col [(tap, ci)][P]; the product lands in the packed weight layout.
+ * b200_colsum: bias / time-embedding gradients; b200_gn_param_grad: GroupNorm affine gradients (per-sample partials);
+ * b200_gemm_f32 / b200_silu_bwd_f32: backward of the time-embedding MLP (models/ncsnpp.py:251-255);
+ * b200_score_loss: SDE / SMLD / DDPM score-matching losses (losses.py:69-163) and their cotangent;
+ * b200_dropout: nn.Dropout in train mode (layerspp.py:265), mask regenerated from (seed, offset, step) for the backward;
+ * b200_grad_sumsq + b200_adam_ema: gradient norm, clipping, Adam and the EMA shadow in one pass over flat buffers. */
+int b200_transpose2d(const void* in, void* out, int dtype, long long R, int C, cudaStream_t stream);
+int b200_im2col_t(const void* x1, int C1, const void* x2, int C2, void* out, int dtype, int B, int H, int W, int Ho, int Wo,
+                  int ksize, int stride, int pad, cudaStream_t stream);
+int b200_colsum(const void* in, float* out, int dtype, int Bn, long long R, int C, long long out_stride, float scale,
+                int accumulate, cudaStream_t stream);
+int b200_gn_param_grad(const void* x1, int C1, const void* x2, int C2, const void* dy, int dtype, int B, int HW, int G,
+                       int nsplit, const float* stats, const float* gamma, const float* beta, float eps, int act,
+                       float* partial, cudaStream_t stream);
+int b200_gemm_f32(float* C, const float* A, const float* B, int M, int N, int K, int ta, int tb, float alpha, float beta,
+                  cudaStream_t stream);
+int b200_silu_f32(float* y, const float* x, long long n, cudaStream_t stream);
+int b200_silu_bwd_f32(float* dx, const float* dy, const float* x, long long n, cudaStream_t stream);
+int b200_score_loss(float* losses, float* loss, float* dout, const float* out, const float* z, const float* alpha,
+                    const float* beta, const float* weight, const float* mul, float r, int B, long long n_per,
+                    cudaStream_t stream);
+int b200_dropout(void* y, const void* x, int dtype, long long n, float p, uint64_t seed, uint64_t offset, const int* step,
+                 cudaStream_t stream);
+int b200_grad_sumsq(float* sumsq, const float* g, long long n, cudaStream_t stream);
+int b200_adam_ema(float* p, float* m, float* v, float* ema, const float* g, const float* hyper, const float* sumsq,
+                  float grad_scale, long long n, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
