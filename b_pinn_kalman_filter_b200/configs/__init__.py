@@ -40,6 +40,8 @@ def _base(image_size, channels, batch, snr, sigma_max, num_scales, dropout, data
         sampling=_cd(method="pc", predictor="reverse_diffusion", corrector="langevin", n_steps_each=1,
                      noise_removal=True, probability_flow=False, snr=snr),
         eval=_cd(batch_size=1024),
+        # configs/default_cifar10_configs.py:58-67 (identical in the lsun / nc defaults)
+        optim=_cd(weight_decay=0, optimizer="Adam", lr=2e-4, beta1=0.9, eps=1e-8, warmup=5000, grad_clip=1.),
         data=_cd(dataset=dataset, image_size=image_size, num_channels=channels, centered=False, random_flip=True,
                  uniform_dequantization=False),
         model=_cd(sigma_min=0.01, sigma_max=sigma_max, num_scales=num_scales, beta_min=0.1, beta_max=20.,

@@ -16,6 +16,8 @@ Builder.finalize sees their uses in the backward half.
                   (op/upfirdn2d.py:24-36 computes the same numbers for the reference's backward)
   image boundary  cotangent NCHW fp32 -> channels-last; image gradient channels-last -> NCHW fp32
 """
+import ctypes
+
 import torch
 
 from .. import _lib
@@ -30,6 +32,16 @@ _lib.register_signature("b200_axpby", [c_vp, c_float, c_vp, c_float, c_vp, c_int
 _lib.register_signature("b200_nearest_up2_bwd_nhwc", [c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_vp])
 _lib.register_signature("b200_zero_stuff2_nhwc", [c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp])
 _lib.register_signature("b200_attention_bwd", [c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_float, c_vp])
+# training (csrc/train.cu)
+_lib.register_signature("b200_transpose2d", [c_vp, c_vp, c_int, c_ll, c_int, c_vp])
+_lib.register_signature("b200_im2col_t", [c_vp, c_int, c_vp, c_int, c_vp, c_int] + [c_int] * 8 + [c_vp])
+_lib.register_signature("b200_colsum", [c_vp, c_vp, c_int, c_int, c_ll, c_int, c_ll, c_float, c_int, c_vp])
+_lib.register_signature("b200_gn_param_grad", [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp,
+                                               c_vp, c_float, c_int, c_vp, c_vp])
+_lib.register_signature("b200_gemm_f32", [c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_float, c_float, c_vp])
+_lib.register_signature("b200_silu_f32", [c_vp, c_vp, c_ll, c_vp])
+_lib.register_signature("b200_silu_bwd_f32", [c_vp, c_vp, c_vp, c_ll, c_vp])
+_lib.register_signature("b200_dropout", [c_vp, c_vp, c_int, c_ll, c_float, ctypes.c_uint64, ctypes.c_uint64, c_vp, c_vp])
 
 
 class _Grads:
@@ -59,14 +71,27 @@ class _Grads:
 def _wt(b, wf, ksize, cin_off, cin_len, scale, rows, k_pad):
     """Backward-data weight [rows][k][k][k_pad] from the forward packed weight wf [cs][k][k][cin_total]:
     Wt[ci][kh][kw][co] = scale * wf[co][k-1-kh][k-1-kw][cin_off + ci]; rows >= cin_len and k_pad >= cs are zero padded."""
+    out = _wt_compute(wf, ksize, cin_off, cin_len, scale, rows, k_pad, _TORCH_DT[b.dt])
+    b.plan.keep.append(out)
+    # training plans re-derive these from the (in place refreshed) forward weights after every optimizer step
+    if not hasattr(b.plan, "wt_recipes"):
+        b.plan.wt_recipes = []
+    b.plan.wt_recipes.append((out, wf, ksize, cin_off, cin_len, scale, rows, k_pad))
+    return out
+
+
+def _wt_compute(wf, ksize, cin_off, cin_len, scale, rows, k_pad, dtype):
     cs = wf.shape[0]
     w = wf.view(cs, ksize, ksize, -1)[:, :, :, cin_off:cin_off + cin_len].to(torch.float32)
     w = w.flip(1, 2).permute(3, 1, 2, 0) * scale
     out = torch.zeros(rows, ksize, ksize, k_pad, device=wf.device, dtype=torch.float32)
     out[:cin_len, :, :, :cs] = w
-    out = out.to(_TORCH_DT[b.dt]).contiguous()
-    b.plan.keep.append(out)
-    return out
+    return out.to(dtype).contiguous()
+
+
+def refresh_dgrad_weights(plan):
+    for out, wf, ksize, cin_off, cin_len, scale, rows, k_pad in getattr(plan, "wt_recipes", ()):
+        out.copy_(_wt_compute(wf, ksize, cin_off, cin_len, scale, rows, k_pad, out.dtype))
 
 
 def _dgrad(b, gy, wf, ksize, cin_off, cin_len, scale, gx, acc):
@@ -108,6 +133,8 @@ def _conv_bwd(b, G, t):
         plan.cot_in = torch.zeros(b.B, t["cout"], x.H, x.W, device=b.e.device, dtype=torch.float32)
         b.emit("b200_nchw_to_nhwc", plan.cot_in.data_ptr(), gy, b.dt, b.B, t["cout"], x.H, x.W, cp, float(t["out_scale"]),
                0.0)
+        if getattr(b.e, "param_grads", False):
+            _conv_param_grads(b, t, gy, 1.0)          # out_scale is already folded into gy by the layout change
         gx, acc = G.target(x)
         _dgrad(b, gy, wf, k, 0, x.C, 1.0, gx, acc)
         return
@@ -115,6 +142,8 @@ def _conv_bwd(b, G, t):
         return                                         # nothing downstream depends on this convolution
     gy = G.get(out)
     scale = float(t["out_scale"])
+    if getattr(b.e, "param_grads", False):
+        _conv_param_grads(b, t, gy, scale)
     if t["res"] is not None:
         gr, acc = G.target(t["res"])
         n = gy.B * gy.H * gy.W * gy.C
@@ -153,6 +182,14 @@ def _gn_bwd(b, G, t):
     b.emit("b200_gn_partial", x, x.C, p2, c2, b.dt, b.B, HW, groups, ns, pf.data_ptr())
     b.emit("b200_gn_bwd_partial", x, x.C, p2, c2, b.dt, b.B, HW, groups, ns, pf.data_ptr(), ga, be, 1e-6, act, gy,
            pb.data_ptr())
+    if getattr(e, "param_grads", False):
+        C = x.C + c2
+        part = b.f32(b.B * C * 2)
+        gsum = b.f32(C * 2)
+        b.emit("b200_gn_param_grad", x, x.C, p2, c2, gy, b.dt, b.B, HW, groups, ns, pf.data_ptr(), ga, be, 1e-6, act,
+               part.data_ptr())
+        b.emit("b200_colsum", part.data_ptr(), gsum.data_ptr(), 0, 1, b.B, 2 * C, 2 * C, 1.0, 0)
+        b.plan.pgrads.append(dict(kind="gn", key=t["key"], buf=gsum, C=C))
     g1, a1 = G.target(x)
     g2, a2 = G.target(x2) if x2 is not None else (None, 0)
     b.emit("b200_gn_bwd_apply", x, x.C, p2, c2, b.dt, b.B, HW, groups, ns, pf.data_ptr(), pb.data_ptr(), ga, be, 1e-6,
@@ -178,9 +215,89 @@ def _upfirdn_bwd(b, G, t):
         b.emit("b200_upfirdn2d_nhwc", gy, k.data_ptr(), gx, b.dt, b.B, gy.H, gy.W, gy.C, 4, 4, down, up, gp0, gp1)
 
 
+def _conv_param_grads(b, t, gy, scale):
+    """Weight / bias / time-embedding gradients of one convolution (b.e.param_grads plans).
+
+    dW[co][(tap, ci)] = sum_p gy[p][co] x[p + tap][ci]: gy^T [Cout][P] (b200_transpose2d) contracted over P with the
+    transposed im2col [(tap, ci)][P] (b200_im2col_t) by the convolution kernels themselves -- a 1x1 "conv" whose fake image
+    is [1, 1, Cout, P] -- so the result lands in the packed weight layout [Cout][kh][kw][Cin_store] (activation dtype).
+    d bias = column sums of gy; the per-sample column sums are also the gradient of the block's Dense_0 output."""
+    from . import tc
+    x, x2, k, stride, pad = t["x"], t["x2"], t["ksize"], t["stride"], t["pad"]
+    Ho, Wo = t["out_hw"]
+    P = b.B * Ho * Wo
+    cin_s = x.C + (x2.C if x2 is not None else 0)
+    cout_s = gy.C
+    kout = k * k * cin_s
+    gyT = Act(None, 1, 1, cout_s, P)
+    xT = Act(None, 1, 1, kout, P)
+    gw = torch.zeros(cout_s, kout, device=b.e.device, dtype=_TORCH_DT[b.dt])
+    b.plan.keep.append(gw)
+    b.emit("b200_transpose2d", gy, gyT, b.dt, P, cout_s)
+    p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+    b.emit("b200_im2col_t", x, x.C, p2, c2, xT, b.dt, b.B, x.H, x.W, Ho, Wo, k, stride, pad[0])
+    flops = 2 * P * cout_s * kout
+    if b.e.use_tc and tc.ENABLED and _lib.lib().b200_conv2d_tc_supported(P, 0, 1, 1, cout_s, kout, 1, 1, 0):
+        b.emit("b200_conv2d_tc", gyT, P, None, 0, xT, None, None, 0, None, 1.0, gw.data_ptr(), 0, None, None, 1, 1, cout_s,
+               kout, 1, flops=flops, tag="wgrad %dx%d %dx%d %d->%d" % (k, k, Ho, Wo, cin_s, cout_s))
+    else:
+        b.emit("b200_conv2d_simt", gyT, P, None, 0, xT, None, None, 0, None, 1.0, gw.data_ptr(), 0, None, b.dt, 1, 1,
+               cout_s, 1, cout_s, kout, 1, 1, 1, 0, 0, flops=flops)
+    # bias: per-sample column sums, then over the batch
+    per = b.f32(b.B * cout_s)
+    gb = b.f32(cout_s)
+    b.emit("b200_colsum", gy, per.data_ptr(), b.dt, b.B, Ho * Wo, cout_s, cout_s, scale, 0)
+    b.emit("b200_colsum", per.data_ptr(), gb.data_ptr(), 0, 1, b.B, cout_s, cout_s, 1.0, 0)
+    if t.get("temb_off") is not None:
+        tm = b.plan.temb
+        if tm["rows"] != b.B:
+            raise RuntimeError("training plans need per-sample time embeddings")
+        dst = b.plan.d_temb_all.data_ptr() + 4 * t["temb_off"]
+        b.emit("b200_colsum", gy, dst, b.dt, b.B, Ho * Wo, t["cout"], tm["total"], scale, 0)
+    cin_true = x.Ct + (x2.Ct if x2 is not None else 0)
+    if x2 is not None and (x.Ct != x.C or x2.Ct != x2.C):
+        raise NotImplementedError("weight gradient of a two-source conv with padded channels")
+    b.plan.pgrads.append(dict(kind="conv", key=t["key"], nin=t["nin"], gw=gw, gb=gb, scale=scale, cout=t["cout"],
+                              cin=cin_true, cin_s=cin_s, k=k))
+
+
+def _temb_param_grads(b):
+    """Backward of the time-embedding MLP and the batched Dense_0 projection (blocks.Net.time_embedding):
+    temb_all = Wcat silu(t2) + bcat, t2 = W1 silu(t1) + b1, t1 = W0 emb + b0 (the Fourier W is frozen in the reference)."""
+    plan, e = b.plan, b.e
+    tm = plan.temb
+    B, H4, total, ed = b.B, tm["hidden"], tm["total"], tm["embed_dim"]
+    wcat, _ = e.packed_dense()
+    d_all = plan.d_temb_all
+    s2, s1 = b.f32(B * H4), b.f32(B * H4)
+    d_s2, d_t2, d_s1, d_t1 = b.f32(B * H4), b.f32(B * H4), b.f32(B * H4), b.f32(B * H4)
+    gwcat, gbcat = b.f32(total * H4), b.f32(total)
+    gw1, gb1, gw0, gb0 = b.f32(H4 * H4), b.f32(H4), b.f32(H4 * ed), b.f32(H4)
+    p = lambda v: v.data_ptr()
+    b.emit("b200_silu_f32", p(s2), p(tm["t2"]), B * H4)
+    b.emit("b200_silu_f32", p(s1), p(tm["t1"]), B * H4)
+    b.emit("b200_gemm_f32", p(gwcat), p(d_all), p(s2), total, H4, B, 1, 0, 1.0, 0.0)          # d_all^T s2
+    b.emit("b200_colsum", p(d_all), p(gbcat), 0, 1, B, total, total, 1.0, 0)
+    b.emit("b200_gemm_f32", p(d_s2), p(d_all), p(wcat), B, H4, total, 0, 0, 1.0, 0.0)          # d_all Wcat
+    b.emit("b200_silu_bwd_f32", p(d_t2), p(d_s2), p(tm["t2"]), B * H4)
+    b.emit("b200_gemm_f32", p(gw1), p(d_t2), p(s1), H4, H4, B, 1, 0, 1.0, 0.0)
+    b.emit("b200_colsum", p(d_t2), p(gb1), 0, 1, B, H4, H4, 1.0, 0)
+    b.emit("b200_gemm_f32", p(d_s1), p(d_t2), e.dev(tm["lin1"] + ".weight"), B, H4, H4, 0, 0, 1.0, 0.0)
+    b.emit("b200_silu_bwd_f32", p(d_t1), p(d_s1), p(tm["t1"]), B * H4)
+    b.emit("b200_gemm_f32", p(gw0), p(d_t1), p(tm["emb"]), H4, ed, B, 1, 0, 1.0, 0.0)
+    b.emit("b200_colsum", p(d_t1), p(gb0), 0, 1, B, H4, H4, 1.0, 0)
+    plan.pgrads.append(dict(kind="dense", gw=gwcat, gb=gbcat))
+    plan.pgrads.append(dict(kind="linear", key=tm["lin1"], gw=gw1, gb=gb1, shape=(H4, H4)))
+    plan.pgrads.append(dict(kind="linear", key=tm["lin0"], gw=gw0, gb=gb0, shape=(H4, ed)))
+
+
 def emit_backward(b):
     """Appends the input-gradient launches to b.plan (call after the forward has been emitted, before finalize)."""
     plan, G = b.plan, _Grads(b)
+    if getattr(b.e, "param_grads", False):
+        plan.pgrads = []
+        tm = plan.temb
+        plan.d_temb_all = torch.zeros(b.B * tm["total"], device=b.e.device, dtype=torch.float32)
     inp = None
     for t in reversed(b.tape):
         kind = t["kind"]
@@ -202,6 +319,12 @@ def emit_backward(b):
                 b.emit("b200_nearest_up2_bwd_nhwc", G.get(t["out"]), gx, b.dt, b.B, x.H, x.W, x.C, acc)
         elif kind == "upfirdn":
             _upfirdn_bwd(b, G, t)
+        elif kind == "dropout":
+            if G.has(t["out"]):
+                gx, acc = G.target(t["x"])
+                assert not acc
+                b.emit("b200_dropout", gx, G.get(t["out"]), b.dt, t["n"], t["p"], b.e.train_seed, t["off"],
+                       b.e.train_step.data_ptr())
         elif kind == "input":
             inp = t
         elif kind == "out_nhwc":
@@ -225,6 +348,8 @@ def emit_backward(b):
         b.emit("b200_axpby", other, 1.0, g, 1.0, g, b.dt, g.B * g.H * g.W * g.C)
     plan.grad_out = torch.zeros(b.B, ch, x.H, x.W, device=b.e.device, dtype=torch.float32)
     b.emit("b200_nhwc_to_nchw", g, plan.grad_out.data_ptr(), b.dt, b.B, ch, x.H, x.W, g.C, None)
+    if getattr(b.e, "param_grads", False):
+        _temb_param_grads(b)
     plan.grad_scale = float(inp["scale"])
     plan.sample_mul_t = b.sample_mul
     _ = DT_BF16

@@ -73,6 +73,8 @@ class Net:
                t1.data_ptr(), Bt, embed_dim, 4 * nf, 0, 0, flops=2 * Bt * embed_dim * 4 * nf)
         b.emit("b200_linear_f32", t1.data_ptr(), e.dev(self.lin1 + ".weight"), e.dev(self.lin1 + ".bias"),
                t2.data_ptr(), Bt, 4 * nf, 4 * nf, 1, 0, flops=2 * Bt * 16 * nf * nf)
+        plan.temb = dict(emb=emb, t1=t1, t2=t2, all=b.temb_all, embed_dim=embed_dim, hidden=4 * nf, total=total, rows=Bt,
+                         lin0=self.lin0, lin1=self.lin1)
         wcat, bcat = e.packed_dense()
         b.emit("b200_linear_f32", t2.data_ptr(), wcat.data_ptr(), bcat.data_ptr(), b.temb_all.data_ptr(), Bt, 4 * nf,
                total, 1, 0, flops=2 * Bt * 4 * nf * total)
@@ -165,7 +167,7 @@ class Net:
             xs = self.fir_up(x) if up else self.fir_down(x)
         off = self.dense(p, out_ch)
         h1 = b.conv(h, p + ".Conv_0", out_ch, 3, temb_off=off)
-        h2 = self.gn_act(h1, p + ".GroupNorm_1", out_ch)
+        h2 = b.dropout(self.gn_act(h1, p + ".GroupNorm_1", out_ch))
         scale = INV_SQRT2 if skip_rescale else 1.0
         if in_ch != out_ch or up or down:
             return b.conv_sc(h2, p + ".Conv_1", p + ".Conv_2", xs, xs2, out_ch, scale, init_scale)
@@ -183,7 +185,7 @@ class Net:
         h = self.gn_act(x, p + ".GroupNorm_0", in_ch, x2=x2, groups=groups)
         off = self.dense(p, out_ch)
         h1 = b.conv(h, p + ".Conv_0", out_ch, 3, temb_off=off)
-        h2 = self.gn_act(h1, p + ".GroupNorm_1", out_ch, groups=groups)
+        h2 = b.dropout(self.gn_act(h1, p + ".GroupNorm_1", out_ch, groups=groups))
         scale = INV_SQRT2 if skip_rescale else 1.0
         if in_ch != out_ch:
             if conv_shortcut:
@@ -210,7 +212,7 @@ class Net:
             w, bias = e.packed_qkv(p, C)
             e.emit_conv(b, hn, None, w, bias, None, None, 1.0, qkv, 1, 1, (0, 0), p + ".qkv")
             b.rec("conv", x=hn, x2=None, out=qkv, w=w, ksize=1, stride=1, pad=(0, 0), res=None, out_scale=1.0,
-                  head=False, cout=3 * C)
+                  head=False, cout=3 * C, key=p, nin="qkv", temb_off=None, out_hw=(x.H, x.W))
         a = b.attention_core(qkv, C)
         scale = INV_SQRT2 if skip_rescale else 1.0
         return b.conv(a, p + ".NIN_3", C, 1, nin=True, init_scale=init_scale, res=x, out_scale=scale)

@@ -307,7 +307,8 @@ class Builder:
             temb_ptr = self.temb_all.data_ptr() + 4 * temb_off
         p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
         self.rec("conv", x=x, x2=x2, out=out, w=w, ksize=ksize, stride=stride, pad=tuple(pad), res=res,
-                 out_scale=out_scale, head=nchw_out is not None, cout=cout)
+                 out_scale=out_scale, head=nchw_out is not None, cout=cout, key=key, nin=nin, temb_off=temb_off,
+                 out_hw=(Ho, Wo))
         if nchw_out is not None:
             from . import tc
             fl = 2 * self.B * Ho * Wo * cout * cin_true * ksize * ksize
@@ -362,6 +363,21 @@ class Builder:
         self.e.sc_fused += 1
         if gn is not None:
             self.e.gn_fused += 1
+        return out
+
+    def dropout(self, x):
+        """nn.Dropout (models/layerspp.py:265, layers.py:646): identity except in a training plan with p > 0."""
+        p = getattr(self.e, "train_dropout", 0.0)
+        if self.dry or self.tape is None or p <= 0.0:
+            return x
+        if isinstance(x, LazyGN):
+            x = self.materialize(x)
+        out = self.new(x.H, x.W, x.C)
+        k = self.e.dropout_layers
+        self.e.dropout_layers += 1
+        n = self.B * x.H * x.W * x.C
+        self.emit("b200_dropout", out, x, self.dt, n, float(p), self.e.train_seed, k << 32, self.e.train_step.data_ptr())
+        self.rec("dropout", x=x, out=out, n=n, p=float(p), off=k << 32)
         return out
 
     def upfirdn(self, x, up, down, pad):
@@ -433,6 +449,8 @@ class ScoreEngine:
         self.workspace = Workspace(self.device)
         self.params = {}           # reference-layout fp32 tensors on device
         self._packed = {}
+        self._recipes = {}         # cache key -> (method name, args): how to rebuild a packed tensor (refresh_packed)
+        self.train_dropout, self.train_seed, self.train_step, self.dropout_layers = 0.0, 0, None, 0
         self._dev = {}
         self._fir = {}
         self.plans = {}
@@ -458,6 +476,7 @@ class ScoreEngine:
             w = torch.cat([self.params[k + ".weight"] for k, _ in self.dense_layout], 0).contiguous()
             bb = torch.cat([self.params[k + ".bias"] for k, _ in self.dense_layout], 0).contiguous()
             self._packed["dense"] = (w, bb)
+            self._recipes["dense"] = ("packed_dense", ())
         return self._packed["dense"]
 
     def packed_qkv(self, p, C):
@@ -467,6 +486,7 @@ class ScoreEngine:
             w = torch.cat([self.params[p + ".NIN_%d.W" % i].t() for i in range(3)], 0)   # [3C, C]
             bb = torch.cat([self.params[p + ".NIN_%d.b" % i] for i in range(3)], 0)
             self._packed[pk] = (w.reshape(3 * C, 1, 1, C).to(_TORCH_DT[self.dt]).contiguous(), bb.contiguous())
+            self._recipes[pk] = ("packed_qkv", (p, C))
         return self._packed[pk]
 
     def load_state_dict(self, sd, strict=True):
@@ -487,6 +507,7 @@ class ScoreEngine:
             new[key] = src.detach().to(device=self.device, dtype=torch.float32).contiguous()
         self.params.update(new)
         self._packed.clear()
+        self._recipes.clear()
         self._dev.clear()
         self.plans.clear()
         self.graphs.clear()
@@ -520,6 +541,7 @@ class ScoreEngine:
             p = torch.zeros(cout_store, kh, kw, cin_store, device=self.device, dtype=torch.float32)
             p[:cout, :, :, :cin] = w.permute(0, 2, 3, 1)
             self._packed[pk] = p.to(_TORCH_DT[self.dt]).contiguous()
+            self._recipes[pk] = ("packed_conv", (key, nin, cin_store, cout_store))
         return self._packed[pk]
 
     def packed_conv_sc(self, key1, key2, nin2, cin, cx, cout):
@@ -536,7 +558,18 @@ class ScoreEngine:
             assert w1.shape == (cout, cin, 3, 3) and w2.shape == (cout, cx), (w1.shape, w2.shape)
             w = torch.cat([w1.permute(0, 2, 3, 1).reshape(cout, 9 * cin), w2], 1)
             self._packed[pk] = (w.to(_TORCH_DT[self.dt]).contiguous(), (self.params[key1 + ".bias"] + b2).contiguous())
+            self._recipes[pk] = ("packed_conv_sc", (key1, key2, nin2, cin, cx, cout))
         return self._packed[pk]
+
+    def refresh_packed(self):
+        """Recomputes every cached packed tensor from `self.params` INTO ITS EXISTING STORAGE (plans hold raw pointers
+        to them): called after an optimizer step has changed the parameters in place."""
+        for pk, (name, args) in list(self._recipes.items()):
+            old = self._packed.pop(pk)
+            new = getattr(self, name)(*args)
+            for o, n in zip(old if isinstance(old, tuple) else (old,), new if isinstance(new, tuple) else (new,)):
+                o.copy_(n)
+            self._packed[pk] = old
 
     def packed_bias(self, key, nin, cout_store):
         pk = (key, "bias", cout_store)
@@ -545,6 +578,7 @@ class ScoreEngine:
             p = torch.zeros(cout_store, device=self.device, dtype=torch.float32)
             p[:b.numel()] = b
             self._packed[pk] = p
+            self._recipes[pk] = ("packed_bias", (key, nin, cout_store))
         return self._packed[pk]
 
     # ---- kernel selection -------------------------------------------------------------------------------------
@@ -591,17 +625,20 @@ class ScoreEngine:
                3 * C, C, float(int(C) ** (-0.5)), flops=4 * b.B * L * L * C)
 
     # ---- plans ------------------------------------------------------------------------------------------------
-    def plan(self, B, grad=False, uniform=False):
+    def plan(self, B, grad=False, uniform=False, train=False):
         """The launch list for batch size B.  grad=True: forward (activations retained) followed by the input-gradient
         pass (models/backward.py); `plan.n_fwd` splits the two.  uniform=True: every sample carries the same label
         (the fused PC loop), so the time-embedding MLP runs on one row."""
-        key = (B, "grad") if grad else ((B, "uniform") if uniform else B)
+        # train=True: a grad plan that also emits parameter gradients (and dropout): models/train.py
+        grad = grad or train
+        key = (B, "train") if train else ((B, "grad") if grad else ((B, "uniform") if uniform else B))
         if key not in self.plans:
             if not self.params:
                 raise RuntimeError("ScoreEngine has no weights; call load_state_dict / init_weights first")
             with torch.cuda.device(self.device):
                 self.spec()
                 self.grad_mode = grad
+                self.param_grads = train
                 self.uniform_mode = uniform and not grad
                 try:
                     b = Builder(self, B, dry=False)
@@ -619,6 +656,7 @@ class ScoreEngine:
                     b.finalize()
                 finally:
                     self.grad_mode = False
+                    self.param_grads = False
                     self.uniform_mode = False
                 self.plans[key] = b.plan
         return self.plans[key]

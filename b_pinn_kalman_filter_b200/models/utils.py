@@ -78,6 +78,11 @@ def init_tensor(shape, init, gen):
     return (torch.rand(shape, generator=gen) * 2. - 1.) * math.sqrt(3 * variance)
 
 
+class ParameterList(list):
+    """`model.parameters()`: a list of tensors that knows which model it came from."""
+    model = None
+
+
 class ScoreModel:
     """The object `create_model` returns; stands where the reference has nn.DataParallel(NCSNpp(config))."""
 
@@ -120,7 +125,22 @@ class ScoreModel:
         self.engine.load_state_dict(sd, strict=strict)
 
     def parameters(self):
-        return [v for k, v in self.engine.params.items() if k != "sigmas"]
+        """The trainable parameters in the reference's `model.parameters()` order (what optimizers and
+        ExponentialMovingAverage index by).  The returned list remembers its model (`.model`)."""
+        tr = getattr(self, "trainer", None)
+        vals = tr.parameters() if tr is not None else [self.engine.params[k] for k in trainable_parameter_order(self.config)]
+        out = ParameterList(vals)
+        out.model = self
+        return out
+
+    def parameters_changed(self):
+        """Parameters were written in place (EMA copy_to / restore): re-derive the packed copies the plans point at."""
+        tr = getattr(self, "trainer", None)
+        if tr is not None:
+            tr.refresh()
+        else:
+            self.engine.refresh_packed()
+            self.engine.version += 1
 
     def to(self, *a, **k):
         return self
@@ -130,9 +150,9 @@ class ScoreModel:
         return self
 
     def train(self, mode=True):
-        if mode:
-            raise NotImplementedError("the B200 engine implements the sampling (eval) path only")
-        self.training = False
+        """Train mode only matters to `losses.get_step_fn` (dropout lives in the training plan, models/train.py);
+        `model(x, labels)` itself is always the inference plan."""
+        self.training = bool(mode)
         return self
 
     def __call__(self, x, labels):

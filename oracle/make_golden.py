@@ -237,6 +237,96 @@ def gen_pc(ns, name):
     print("pc", name, "out rms", float(x.pow(2).mean().sqrt()), "nfe", nfe)
 
 
+TRAIN_CASES = {
+    # name: (score case it is built on, loss kind, reduce_mean, likelihood_weighting)
+    "ve_sde": ("tiny_fourier_residual", "sde", False, False),
+    "ve_sde_lw_mean_skip": ("tiny_output_skip", "sde", True, True),
+    "vp_ddpm": ("tiny_positional_vp", "ddpm", True, False),
+}
+TRAIN_OPT = dict(lr=2e-3, beta1=0.9, eps=1e-8, weight_decay=0.0, warmup=2, grad_clip=1.0, ema=0.999, steps=3)
+
+
+def train_probe(i, shape):
+    """Seeded direction a gradient / parameter is projected on (both sides build the same one)."""
+    return torch.randn(shape, generator=torch.Generator().manual_seed(7000 + i))
+
+
+def gen_train(ns, name):
+    """Three steps of the reference's step_fn (losses.py:191-222) on the tiny network with dropout 0 and injected
+    (t, z): loss_fn is restated from losses.py:94-110 / 149-160 around the reference's OWN model, get_score_fn,
+    torch.optim.Adam and models/ema.py (losses.py itself imports the absent bayesian_torch); optimize_fn = warm-up +
+    clip_grad_norm_ + step as losses.py:57-63."""
+    import importlib
+    ref_ema = importlib.import_module("models.ema")
+    base, kind, reduce_mean, lw = TRAIN_CASES[name]
+    our, refm, over, _ = SCORE_CASES[base]
+    cfg, rcfg = tiny_pair(our, refm, over)
+    rcfg.model.dropout = 0.
+    spec, _ = parameter_spec(cfg, mutils.get_model(cfg.model.name))
+    sd = weights.trained_like_state_dict(spec, cfg, seed=4321)
+    model = ns.mutils.create_model(rcfg)
+    model.load_state_dict({"module." + k: v for k, v in sd.items()})
+    sde, _ = ref_import.get_sde(ns, rcfg)
+    B, o = 2, TRAIN_OPT
+    S, C = cfg.data.image_size, cfg.data.num_channels
+    gen = torch.Generator().manual_seed(555)
+    names = [n[len("module."):] for n, p in model.named_parameters() if p.requires_grad]
+    params = [p for p in model.parameters() if p.requires_grad]
+    optimizer = torch.optim.Adam(model.parameters(), lr=o["lr"], betas=(o["beta1"], 0.999), eps=o["eps"],
+                                 weight_decay=o["weight_decay"])
+    ema = ref_ema.ExponentialMovingAverage(model.parameters(), decay=o["ema"])
+    reduce_op = torch.mean if reduce_mean else (lambda *a, **k: 0.5 * torch.sum(*a, **k))
+    out = {"names": np.array(names)}
+    losses, ts, zs, batches = [], [], [], []
+    for step in range(o["steps"]):
+        batch = torch.rand(B, C, S, S, generator=gen)
+        z = torch.randn(B, C, S, S, generator=gen)
+        optimizer.zero_grad()
+        if kind == "sde":
+            t = torch.rand(B, generator=gen) * (sde.T - 1e-5) + 1e-5
+            score_fn = ns.mutils.get_score_fn(sde, model, train=True, continuous=True)
+            mean, std = sde.marginal_prob(batch, t)
+            score = score_fn(mean + std[:, None, None, None] * z, t)
+            if not lw:
+                l = torch.square(score * std[:, None, None, None] + z)
+                l = reduce_op(l.reshape(B, -1), dim=-1)
+            else:
+                g2 = sde.sde(torch.zeros_like(batch), t)[1] ** 2
+                l = torch.square(score + z / std[:, None, None, None])
+                l = reduce_op(l.reshape(B, -1), dim=-1) * g2
+        else:
+            t = torch.randint(0, sde.N, (B,), generator=gen)
+            model_fn = ns.mutils.get_model_fn(model, train=True)
+            sa, s1 = sde.sqrt_alphas_cumprod, sde.sqrt_1m_alphas_cumprod
+            score = model_fn(sa[t, None, None, None] * batch + s1[t, None, None, None] * z, t)
+            l = reduce_op(torch.square(score - z).reshape(B, -1), dim=-1)
+        loss = torch.mean(l)
+        loss.backward()
+        if step == 0:
+            out["gnorm"] = np.array([float(p.grad.norm()) for p in params])
+            out["gproj"] = np.array([float((p.grad * train_probe(i, p.shape)).sum()) for i, p in enumerate(params)])
+            for tag, key in (("first", names[0]), ("mid", names[len(names) // 2]), ("last", names[-2])):
+                out["gfull_" + tag] = params[names.index(key)].grad.numpy().copy()
+                out["gfull_" + tag + "_key"] = np.array(key)
+        lr = o["lr"] * np.minimum(step / o["warmup"], 1.0)
+        for g in optimizer.param_groups:
+            g["lr"] = lr
+        torch.nn.utils.clip_grad_norm_(model.parameters(), max_norm=o["grad_clip"])
+        optimizer.step()
+        ema.update(model.parameters())
+        losses.append(float(loss)); ts.append(t.numpy()); zs.append(z.numpy()); batches.append(batch.numpy())
+    with torch.no_grad():
+        p0 = [sd[n] for n in names]
+        out["dnorm"] = np.array([float((p - q).norm()) for p, q in zip(params, p0)])
+        out["dproj"] = np.array([float(((p - q) * train_probe(i, p.shape)).sum()) for i, (p, q) in enumerate(zip(params, p0))])
+        out["eproj"] = np.array([float(((s - q) * train_probe(i, s.shape)).sum())
+                                 for i, (s, q) in enumerate(zip(ema.shadow_params, p0))])
+        out["enorm"] = np.array([float((s - q).norm()) for s, q in zip(ema.shadow_params, p0)])
+    np.savez_compressed(os.path.join(GOLDEN, "train_%s.npz" % name), losses=np.array(losses), t=np.stack(ts), z=np.stack(zs),
+                        batch=np.stack(batches), weight_seed=4321, **out)
+    print("train", name, "losses", losses, "grad norm", float(np.sqrt((out["gnorm"] ** 2).sum())))
+
+
 def gen_ctrl(ns, kind):
     """Inpainting / colorisation with the REFERENCE's controllable_generation.py (:8-180) on the tiny VE network, the
     same injected noise stream as gen_pc (prior, then per step: corrector, mix, predictor, mix)."""
@@ -361,6 +451,9 @@ def main():
     for n in PC_CASES:
         if a.only in (None, "pc", n):
             gen_pc(ns, n)
+    for n in TRAIN_CASES:
+        if a.only in (None, "train", "train_" + n):
+            gen_train(ns, n)
     for kind in ("inpaint", "colorize"):
         if a.only in (None, "ctrl", "ctrl_" + kind):
             gen_ctrl(ns, kind)

@@ -145,3 +145,31 @@ def ctrl_case(kind):
     t = lambda k: torch.from_numpy(g[k])
     return dict(cfg=cfg, sd=sd, out=t("out"), data=t("data"), mask=t("mask"), gray=t("gray"), N=int(g["N"]),
                 eps=float(g["eps"]), noise_seed=int(g["noise_seed"]), shape=tuple(g["data"].shape))
+
+
+TRAIN_CASES = {
+    # name: (score case it is built on, loss kind, reduce_mean, likelihood_weighting)   (oracle/make_golden.py gen_train)
+    "ve_sde": ("tiny_fourier_residual", "sde", False, False),
+    "ve_sde_lw_mean_skip": ("tiny_output_skip", "sde", True, True),
+    "vp_ddpm": ("tiny_positional_vp", "ddpm", True, False),
+}
+TRAIN_OPT = dict(lr=2e-3, beta1=0.9, eps=1e-8, weight_decay=0.0, warmup=2, grad_clip=1.0, ema=0.999, steps=3)
+
+
+def train_probe(i, shape):
+    return torch.randn(shape, generator=torch.Generator().manual_seed(7000 + i))
+
+
+def train_case(name):
+    """-> dict(cfg, sd, kind, reduce_mean, lw, golden npz) for three reference training steps with injected (t, z)."""
+    base, kind, reduce_mean, lw = TRAIN_CASES[name]
+    our, over, _ = SCORE_CASES[base]
+    cfg = our_config(our, over)
+    cfg.model.dropout = 0.
+    o = TRAIN_OPT
+    cfg.optim.update(lr=o["lr"], beta1=o["beta1"], eps=o["eps"], weight_decay=o["weight_decay"], warmup=o["warmup"],
+                     grad_clip=o["grad_clip"])
+    cfg.model.ema_rate = o["ema"]
+    g = np.load(os.path.join(GOLDEN, "train_%s.npz" % name))
+    sd = state_dict_for(cfg, int(g["weight_seed"]))
+    return dict(cfg=cfg, sd=sd, kind=kind, reduce_mean=reduce_mean, lw=lw, g=g)

@@ -1,0 +1,166 @@
+"""The training step (b_pinn_kalman_filter_b200/losses.py + models/train.py + csrc/train.cu) against three steps of the
+reference's step_fn run by oracle/make_golden.py (reference model / get_score_fn / torch.optim.Adam / models/ema.py,
+dropout 0, injected t and z): loss values, the gradient of EVERY parameter after the first backward (norm and a seeded
+projection, three tensors in full), and the parameter / EMA-shadow movement after three optimizer steps."""
+import numpy as np
+import pytest
+import torch
+
+import cases
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(c, dev, precision):
+    from b_pinn_kalman_filter_b200 import losses, sde_lib
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    from b_pinn_kalman_filter_b200.models.ema import ExponentialMovingAverage
+    cfg = c["cfg"]
+    m = mutils.ScoreModel(cfg, device=dev, precision=precision, init=False)
+    m.load_state_dict(c["sd"])
+    mm = cfg.model
+    if cfg.training.sde == "vesde":
+        sde = sde_lib.VESDE(mm.sigma_min, mm.sigma_max, mm.num_scales)
+    else:
+        sde = sde_lib.VPSDE(mm.beta_min, mm.beta_max, mm.num_scales)
+    state = dict(optimizer=losses.get_optimizer(cfg, m.parameters()), model=m,
+                 ema=ExponentialMovingAverage(m.parameters(), decay=mm.ema_rate), step=0)
+    step_fn = losses.get_step_fn(sde, train=True, optimize_fn=losses.optimization_manager(cfg), reduce_mean=c["reduce_mean"],
+                                 continuous=c["kind"] == "sde", likelihood_weighting=c["lw"])
+    return m, sde, state, step_fn
+
+
+@pytest.mark.parametrize("name", sorted(cases.TRAIN_CASES))
+@pytest.mark.parametrize("precision,gtol,ltol", [("fp32", 2e-3, 1e-4), ("bf16", 6e-2, 2e-2)])
+def test_training_steps_match_reference(cuda, name, precision, gtol, ltol):
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    c = cases.train_case(name)
+    g = c["g"]
+    m, sde, state, step_fn = _setup(c, cuda, precision)
+    names = [str(n) for n in g["names"]]
+    assert names == mutils.trainable_parameter_order(c["cfg"])          # the reference's model.parameters() order
+    p0 = [c["sd"][n].to(cuda) for n in names]
+    losses_got = []
+    for step in range(cases.TRAIN_OPT["steps"]):
+        t = torch.from_numpy(g["t"][step]).to(cuda)
+        loss = step_fn(state, torch.from_numpy(g["batch"][step]).to(cuda), t=t, z=torch.from_numpy(g["z"][step]).to(cuda))
+        losses_got.append(float(loss))
+        if step == 0:
+            tr = m.trainer
+            grads = tr.grads()
+            gn = np.array([float(grads[k].norm()) for k in names])
+            gp = np.array([float((grads[k].cpu() * cases.train_probe(i, grads[k].shape)).sum()) for i, k in enumerate(names)])
+            total = float(np.sqrt((g["gnorm"] ** 2).sum()))
+            # per parameter, relative to that parameter's own gradient norm (floor: 1e-4 of the total norm)
+            scale = np.maximum(g["gnorm"], 1e-4 * total)
+            bad = np.nonzero((np.abs(gn - g["gnorm"]) > gtol * scale) | (np.abs(gp - g["gproj"]) > 3 * gtol * scale))[0]
+            assert len(bad) == 0, [(names[i], gn[i], g["gnorm"][i], gp[i], g["gproj"][i]) for i in bad[:6]]
+            for tag in ("first", "mid", "last"):
+                key = str(g["gfull_%s_key" % tag])
+                ref = torch.from_numpy(g["gfull_" + tag])
+                assert cases.rel_l2(grads[key].cpu(), ref) < 5 * gtol, (key, cases.rel_l2(grads[key].cpu(), ref))
+    assert state["step"] == 3
+    np.testing.assert_allclose(losses_got, g["losses"], rtol=ltol)
+    # parameter and EMA movement after three steps (step 0 has lr = 0 by the warm-up rule: losses.py:57-59)
+    params = m.parameters()
+    shadow = state["ema"].shadow_params
+    dtol = 3e-2 if precision == "fp32" else 0.35          # Adam's early updates are ~ lr * sign(g): sign flips of tiny g
+    dn = np.array([float((p - q).norm()) for p, q in zip(params, p0)])
+    en = np.array([float((s - q).norm()) for s, q in zip(shadow, p0)])
+    assert np.all(np.abs(dn - g["dnorm"]) <= dtol * np.maximum(g["dnorm"], 1e-12)), np.abs(dn / g["dnorm"] - 1).max()
+    assert np.all(np.abs(en - g["enorm"]) <= dtol * np.maximum(g["enorm"], 1e-12)), np.abs(en / g["enorm"] - 1).max()
+    if precision == "fp32":
+        dp = np.array([float(((p - q).cpu() * cases.train_probe(i, p.shape)).sum()) for i, (p, q) in enumerate(zip(params, p0))])
+        assert np.all(np.abs(dp - g["dproj"]) <= 0.1 * g["dnorm"] + 1e-12)
+    # the model the sampler sees has moved with the parameters (packed weights refreshed in place)
+    x = torch.from_numpy(g["batch"][0]).to(cuda)
+    lab = torch.full((x.shape[0],), 1.0, device=cuda)
+    y1 = m(x, lab)
+    from b_pinn_kalman_filter_b200.models import utils as mu
+    m2 = mu.ScoreModel(c["cfg"], device=cuda, precision=precision, init=False)
+    sd2 = dict(c["sd"])
+    sd2.update({k: v.clone() for k, v in zip(names, params)})
+    m2.load_state_dict(sd2)
+    assert cases.rel_l2(y1.cpu(), m2(x, lab).cpu()) < (1e-5 if precision == "fp32" else 2e-2)
+
+
+def test_eval_step_uses_ema_weights_and_restores(cuda):
+    from b_pinn_kalman_filter_b200 import losses
+    c = cases.train_case("ve_sde")
+    g = c["g"]
+    m, sde, state, step_fn = _setup(c, cuda, "fp32")
+    batch, t, z = (torch.from_numpy(g[k][0]).to(cuda) for k in ("batch", "t", "z"))
+    for _ in range(2):
+        step_fn(state, batch, t=torch.from_numpy(g["t"][1]).to(cuda), z=z)
+    eval_fn = losses.get_step_fn(sde, train=False, reduce_mean=False, continuous=True, likelihood_weighting=False)
+    before = [p.clone() for p in m.parameters()]
+    le = float(eval_fn(state, batch, t=t, z=z))
+    after = m.parameters()
+    assert all(torch.equal(a, b) for a, b in zip(before, after))
+    assert np.isfinite(le) and le > 0
+    # at eval time the EMA weights are (almost) the initial ones: the loss is close to the reference's first loss
+    assert abs(le - float(g["losses"][0])) < 0.05 * float(g["losses"][0])
+
+
+def test_dropout_mask_statistics_and_backward(cuda):
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import backward  # noqa: F401  (registers b200_dropout)
+    lib = _lib.lib()
+    n, p = 1 << 20, 0.1
+    x = torch.ones(n, device=cuda)
+    step = torch.zeros(1, device=cuda, dtype=torch.int32)
+    ys = []
+    for s in (0, 0, 1):
+        step.fill_(s)
+        y = torch.empty_like(x)
+        _lib.check(lib.b200_dropout(_lib.ptr(y), _lib.ptr(x), 0, n, p, 11, 5 << 32, _lib.ptr(step), _lib.stream()), "dropout")
+        ys.append(y)
+    torch.cuda.synchronize()
+    assert torch.equal(ys[0], ys[1]) and not torch.equal(ys[0], ys[2])           # same step: same mask; next step: new one
+    frac = float((ys[0] == 0).float().mean())
+    assert abs(frac - p) < 5 * (p * (1 - p) / n) ** 0.5
+    kept = ys[0][ys[0] != 0]
+    assert torch.allclose(kept, torch.full_like(kept, 1 / (1 - p)))
+    assert abs(float(ys[0].mean()) - 1.0) < 2e-3
+    # a training step with dropout 0.1 runs, is finite, and differs from the dropout-free loss
+    c = cases.train_case("ve_sde")
+    c["cfg"].model.dropout = 0.1
+    m, sde, state, step_fn = _setup(c, cuda, "bf16")
+    g = c["g"]
+    l = float(step_fn(state, torch.from_numpy(g["batch"][0]).to(cuda), t=torch.from_numpy(g["t"][0]).to(cuda),
+                      z=torch.from_numpy(g["z"][0]).to(cuda)))
+    assert np.isfinite(l) and abs(l - float(g["losses"][0])) > 1e-3 * float(g["losses"][0])
+    assert all(torch.isfinite(v).all() for v in m.trainer.grads().values())
+
+
+@pytest.mark.parametrize("shape", [(16, 32, 32, 128, 0, 128, 3, 1), (8, 16, 16, 256, 256, 256, 3, 1), (8, 16, 16, 512, 0, 256, 1, 1),
+                                   (4, 33, 33, 64, 0, 128, 3, 2)])
+def test_weight_gradient_on_the_tensor_core_conv(cuda, shape):
+    """dW through b200_transpose2d + b200_im2col_t + b200_conv2d_tc against torch.nn.grad.conv2d_weight (fp32 on the same
+    bf16-rounded operands)."""
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import backward, tc  # noqa: F401
+    B, H, W, C1, C2, Cout, k, stride = shape
+    lib = _lib.lib()
+    gen = torch.Generator().manual_seed(sum(shape))
+    pad = k // 2 if stride == 1 else 0
+    Ho = (H + 2 * pad - k) // stride + 1
+    x1 = torch.randn(B, H, W, C1, generator=gen).to(cuda, torch.bfloat16)
+    x2 = torch.randn(B, H, W, C2, generator=gen).to(cuda, torch.bfloat16) if C2 else None
+    gy = torch.randn(B, Ho, Ho, Cout, generator=gen).to(cuda, torch.bfloat16)
+    P, Ct = B * Ho * Ho, C1 + C2
+    gyT = torch.empty(Cout, P, device=cuda, dtype=torch.bfloat16)
+    xT = torch.empty(k * k * Ct, P, device=cuda, dtype=torch.bfloat16)
+    gw = torch.empty(Cout, k * k * Ct, device=cuda, dtype=torch.bfloat16)
+    st = _lib.stream()
+    _lib.check(lib.b200_transpose2d(_lib.ptr(gy), _lib.ptr(gyT), 1, P, Cout, st), "transpose")
+    _lib.check(lib.b200_im2col_t(_lib.ptr(x1), C1, _lib.ptr(x2), C2, _lib.ptr(xT), 1, B, H, W, Ho, Ho, k, stride, pad, st), "im2col_t")
+    assert lib.b200_conv2d_tc_supported(P, 0, 1, 1, Cout, k * k * Ct, 1, 1, 0) == 1
+    _lib.check(lib.b200_conv2d_tc(_lib.ptr(gyT), P, None, 0, _lib.ptr(xT), None, None, 0, None, 1.0, _lib.ptr(gw), 0, None,
+                                  None, 1, 1, Cout, k * k * Ct, 1, st), "conv2d_tc (wgrad)")
+    torch.cuda.synchronize()
+    assert torch.equal(gyT, gy.reshape(P, Cout).t())
+    xx = (torch.cat([x1, x2], -1) if C2 else x1).float().permute(0, 3, 1, 2)
+    ref = torch.nn.grad.conv2d_weight(xx, (Cout, Ct, k, k), gy.float().permute(0, 3, 1, 2), stride=stride, padding=pad)
+    got = gw.float().view(Cout, k, k, Ct).permute(0, 3, 1, 2)
+    assert cases.rel_l2(got.cpu(), ref.cpu()) < 4e-3, cases.rel_l2(got.cpu(), ref.cpu())
