@@ -67,11 +67,19 @@ def test_training_steps_match_reference(cuda, name, precision, gtol, ltol):
     dtol = 3e-2 if precision == "fp32" else 0.35          # Adam's early updates are ~ lr * sign(g): sign flips of tiny g
     dn = np.array([float((p - q).norm()) for p, q in zip(params, p0)])
     en = np.array([float((s - q).norm()) for s, q in zip(shadow, p0)])
-    assert np.all(np.abs(dn - g["dnorm"]) <= dtol * np.maximum(g["dnorm"], 1e-12)), np.abs(dn / g["dnorm"] - 1).max()
-    assert np.all(np.abs(en - g["enorm"]) <= dtol * np.maximum(g["enorm"], 1e-12)), np.abs(en / g["enorm"] - 1).max()
+    # Parameters whose TRUE gradient is zero (the attention key bias NIN_1.b: softmax is invariant to it) receive pure
+    # round-off noise, which Adam's m / sqrt(v) turns into full-size steps of arbitrary sign -- in the reference as well
+    # as here.  They are recognised by a first-step gradient norm 1e-5 below the median and left out.
+    live = g["gnorm"] > 1e-5 * np.median(g["gnorm"])
+    assert live.sum() >= len(names) - 8, [n for n, l in zip(names, live) if not l]
+    bad = np.nonzero(live & (np.abs(dn - g["dnorm"]) > dtol * np.maximum(g["dnorm"], 1e-12)))[0]
+    assert len(bad) == 0, [(names[i], dn[i], g["dnorm"][i], g["gnorm"][i]) for i in bad[:6]]
+    bad = np.nonzero(live & (np.abs(en - g["enorm"]) > dtol * np.maximum(g["enorm"], 1e-12)))[0]
+    assert len(bad) == 0, [(names[i], en[i], g["enorm"][i]) for i in bad[:6]]
     if precision == "fp32":
         dp = np.array([float(((p - q).cpu() * cases.train_probe(i, p.shape)).sum()) for i, (p, q) in enumerate(zip(params, p0))])
-        assert np.all(np.abs(dp - g["dproj"]) <= 0.1 * g["dnorm"] + 1e-12)
+        bad = np.nonzero(live & (np.abs(dp - g["dproj"]) > 0.1 * g["dnorm"] + 1e-12))[0]
+        assert len(bad) == 0, [(names[i], dp[i], g["dproj"][i], g["dnorm"][i]) for i in bad[:6]]
     # the model the sampler sees has moved with the parameters (packed weights refreshed in place)
     x = torch.from_numpy(g["batch"][0]).to(cuda)
     lab = torch.full((x.shape[0],), 1.0, device=cuda)
@@ -96,10 +104,24 @@ def test_eval_step_uses_ema_weights_and_restores(cuda):
     before = [p.clone() for p in m.parameters()]
     le = float(eval_fn(state, batch, t=t, z=z))
     after = m.parameters()
-    assert all(torch.equal(a, b) for a, b in zip(before, after))
+    assert all(torch.equal(a, b) for a, b in zip(before, after))          # ema.restore put the raw parameters back
     assert np.isfinite(le) and le > 0
-    # at eval time the EMA weights are (almost) the initial ones: the loss is close to the reference's first loss
-    assert abs(le - float(g["losses"][0])) < 0.05 * float(g["losses"][0])
+    # the same loss from a fresh model that HOLDS the EMA shadow as its weights, and from one holding the raw weights
+    from b_pinn_kalman_filter_b200.models import utils as mutils
+    from b_pinn_kalman_filter_b200.models.ema import ExponentialMovingAverage
+    names = mutils.trainable_parameter_order(c["cfg"])
+
+    def loss_with(weights):
+        sd = dict(c["sd"])
+        sd.update({k: v.clone() for k, v in zip(names, weights)})
+        m2 = mutils.ScoreModel(c["cfg"], device=cuda, precision="fp32", init=False)
+        m2.load_state_dict(sd)
+        st2 = dict(model=m2, ema=ExponentialMovingAverage(m2.parameters(), decay=0.999), step=0, optimizer=None)
+        return float(eval_fn(st2, batch, t=t, z=z))
+
+    l_ema, l_raw = loss_with(state["ema"].shadow_params), loss_with(after)
+    assert abs(le - l_ema) <= 1e-5 * l_ema, (le, l_ema)
+    assert abs(le - l_raw) > 1e-4 * l_raw, (le, l_raw)
 
 
 def test_dropout_mask_statistics_and_backward(cuda):
@@ -134,7 +156,7 @@ def test_dropout_mask_statistics_and_backward(cuda):
 
 
 @pytest.mark.parametrize("shape", [(16, 32, 32, 128, 0, 128, 3, 1), (8, 16, 16, 256, 256, 256, 3, 1), (8, 16, 16, 512, 0, 256, 1, 1),
-                                   (4, 33, 33, 64, 0, 128, 3, 2)])
+                                   (4, 17, 17, 128, 0, 256, 3, 2)])
 def test_weight_gradient_on_the_tensor_core_conv(cuda, shape):
     """dW through b200_transpose2d + b200_im2col_t + b200_conv2d_tc against torch.nn.grad.conv2d_weight (fp32 on the same
     bf16-rounded operands)."""
