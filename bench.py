@@ -353,6 +353,34 @@ def other_config_measurements(dev, timeit):
                            "finite": bool(torch.isfinite(host_out).all())}
         del m, plan
         torch.cuda.empty_cache()
+    # training step (losses.get_step_fn with train=True): C3 network, bf16, 128 images per GPU (= 1024 over
+    # 8 GPUs), dropout 0.1, Adam + EMA; forward + loss + input-gradient chain + parameter gradients + fused optimizer
+    try:
+        from b_pinn_kalman_filter_b200 import losses, sde_lib
+        from b_pinn_kalman_filter_b200.models.ema import ExponentialMovingAverage
+        cfg = configs.get_config(CONFIG)
+        cfg.device = dev
+        mt = mutils.ScoreModel(cfg, device=dev, precision="bf16", init=False)
+        mt.init_weights(42, zero_init_scale=1.0)
+        sde_t = sde_lib.VESDE(cfg.model.sigma_min, cfg.model.sigma_max, cfg.model.num_scales)
+        state = dict(optimizer=losses.get_optimizer(cfg, mt.parameters()), model=mt,
+                     ema=ExponentialMovingAverage(mt.parameters(), decay=cfg.model.ema_rate), step=0)
+        fn = losses.get_step_fn(sde_t, train=True, optimize_fn=losses.optimization_manager(cfg), reduce_mean=False,
+                                continuous=True, likelihood_weighting=False)
+        Bt = 128
+        xb = torch.rand(Bt, 3, 32, 32, device=dev)
+        l0 = float(fn(state, xb))
+        ms = timeit(lambda: fn(state, xb), iters=5)
+        tr = mt.trainer
+        res["C3_training_step"] = {"batch": Bt, "ms_per_step": ms, "images_per_s": Bt / ms * 1e3, "loss_first": l0,
+                                   "loss_last": float(tr.loss[0]), "launches": len(tr.plan.ops),
+                                   "parameters": tr.n, "finite": bool(torch.isfinite(tr.flat_p).all()),
+                                   "note": "weight gradients on b200_conv2d_tc over K = pixels; per-step weight "
+                                           "re-packing and gradient re-layout are torch copies (host-bound)"}
+        del mt, state, tr
+        torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001
+        res["C3_training_step"] = {"unavailable": repr(e)[:200]}
     cfg = configs.get_config("inverse/nc_ddpmpp_inpaint_dps")
     cfg.device = dev
     m = mutils.ScoreModel(cfg, device=dev, precision="bf16", init=False)

@@ -24,6 +24,11 @@ def _free_port():
     return p
 
 
+def sde_lib_mod():
+    from b_pinn_kalman_filter_b200 import sde_lib
+    return sde_lib
+
+
 def _loop(m, c, N, B, **kw):
     from b_pinn_kalman_filter_b200 import sampling, sde_lib
     sampling.set_seed(31)          # same Philox key AND the same block of stream ids for every loop built here
@@ -79,6 +84,32 @@ def _worker(rank, world, port, q):
             sl = xw[rank * (B // world):(rank + 1) * (B // world)]
             out[precision] = (bool(torch.equal(part.x, sl)), float((part.x - sl).abs().max()), part.graph is not None,
                               part.xchg is not None, bool(torch.isfinite(part.x).all()))
+        # ---- data-parallel training: 2 ranks x 2 samples (bucketed NCCL all-reduce of the flat gradient, mean folded
+        # into the optimizer kernel) against one rank x 4 samples -- the same parameters after one optimizer step
+        import numpy as np
+        from b_pinn_kalman_filter_b200 import losses
+        from b_pinn_kalman_filter_b200.models import train as train_mod
+        from b_pinn_kalman_filter_b200.models.ema import ExponentialMovingAverage
+        tc_ = cases.train_case("ve_sde")
+        tc_["cfg"].optim.warmup = 0
+        g = tc_["g"]
+        xb = torch.from_numpy(np.concatenate([g["batch"][0], g["batch"][1]])).to(dev)
+        zb = torch.from_numpy(np.concatenate([g["z"][0], g["z"][1]])).to(dev)
+        tb = torch.from_numpy(np.concatenate([g["t"][0], g["t"][1]])).to(dev)
+        train_mod.BUCKET_BYTES = 256 << 10          # several buckets even for the tiny network
+        res = []
+        for group, sl in ((None, slice(0, 4)), (pg, slice(2 * rank, 2 * rank + 2))):
+            mt = mutils.ScoreModel(tc_["cfg"], device=dev, precision="fp32", init=False)
+            mt.load_state_dict(tc_["sd"])
+            sde_t = sde_lib_mod().VESDE(tc_["cfg"].model.sigma_min, tc_["cfg"].model.sigma_max, tc_["cfg"].model.num_scales)
+            state = dict(optimizer=losses.get_optimizer(tc_["cfg"], mt.parameters()), model=mt,
+                         ema=ExponentialMovingAverage(mt.parameters(), decay=0.999), step=0)
+            fn = losses.get_step_fn(sde_t, train=True, optimize_fn=losses.optimization_manager(tc_["cfg"]),
+                                    reduce_mean=False, continuous=True, likelihood_weighting=False, process_group=group)
+            fn(state, xb[sl], t=tb[sl], z=zb[sl])
+            res.append(torch.cat([p.reshape(-1) for p in mt.parameters()]).clone())
+        moved = float((res[0] - torch.cat([tc_["sd"][k].reshape(-1) for k in mt.trainer.keys]).to(dev)).norm())
+        out["ddp"] = (float((res[0] - res[1]).norm()) / moved, moved, mt.trainer.world)
         dist.barrier()
     finally:
         q.put(out)
@@ -106,3 +137,6 @@ def test_sharded_loop_equals_unsharded_slice_on_two_gpus(cuda):
             equal, diff, graphed, xchg, finite = r[precision]
             assert finite and xchg and graphed, (precision, r)
             assert equal, (precision, diff, r)
+        rel, moved, world = r["ddp"]
+        assert world == 2 and moved > 0
+        assert rel < 2e-3, r["ddp"]      # Adam turns 1e-6 gradient differences (summation order) into 1e-3 of one step
