@@ -229,20 +229,28 @@ def _conv_param_grads(b, t, gy, scale):
     cin_s = x.C + (x2.C if x2 is not None else 0)
     cout_s = gy.C
     kout = k * k * cin_s
+    # column count padded to the tensor-core tile (stem-type shapes: 9 * 64 = 576 -> 640); the extra rows of the
+    # transposed im2col stay zero (allocated zeroed, never written) and the extra gradient columns are ignored
+    kpad = (kout + 127) // 128 * 128 if b.e.use_tc else kout
     gyT = Act(None, 1, 1, cout_s, P)
-    xT = Act(None, 1, 1, kout, P)
-    gw = torch.zeros(cout_s, kout, device=b.e.device, dtype=_TORCH_DT[b.dt])
+    if kpad != kout:
+        xT_t = torch.zeros(kpad * P, device=b.e.device, dtype=_TORCH_DT[b.dt])
+        b.plan.keep.append(xT_t)
+        xT = xT_t.data_ptr()
+    else:
+        xT = Act(None, 1, 1, kout, P)
+    gw = torch.zeros(cout_s, kpad, device=b.e.device, dtype=_TORCH_DT[b.dt])
     b.plan.keep.append(gw)
     b.emit("b200_transpose2d", gy, gyT, b.dt, P, cout_s)
     p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
     b.emit("b200_im2col_t", x, x.C, p2, c2, xT, b.dt, b.B, x.H, x.W, Ho, Wo, k, stride, pad[0])
     flops = 2 * P * cout_s * kout
-    if b.e.use_tc and tc.ENABLED and _lib.lib().b200_conv2d_tc_supported(P, 0, 1, 1, cout_s, kout, 1, 1, 0):
+    if b.e.use_tc and tc.ENABLED and _lib.lib().b200_conv2d_tc_supported(P, 0, 1, 1, cout_s, kpad, 1, 1, 0):
         b.emit("b200_conv2d_tc", gyT, P, None, 0, xT, None, None, 0, None, 1.0, gw.data_ptr(), 0, None, None, 1, 1, cout_s,
-               kout, 1, flops=flops, tag="wgrad %dx%d %dx%d %d->%d" % (k, k, Ho, Wo, cin_s, cout_s))
+               kpad, 1, flops=flops, tag="wgrad %dx%d %dx%d %d->%d" % (k, k, Ho, Wo, cin_s, cout_s))
     else:
         b.emit("b200_conv2d_simt", gyT, P, None, 0, xT, None, None, 0, None, 1.0, gw.data_ptr(), 0, None, b.dt, 1, 1,
-               cout_s, 1, cout_s, kout, 1, 1, 1, 0, 0, flops=flops)
+               cout_s, 1, cout_s, kpad, 1, 1, 1, 0, 0, flops=flops)
     # bias: per-sample column sums, then over the batch
     per = b.f32(b.B * cout_s)
     gb = b.f32(cout_s)
@@ -258,7 +266,7 @@ def _conv_param_grads(b, t, gy, scale):
     if x2 is not None and (x.Ct != x.C or x2.Ct != x2.C):
         raise NotImplementedError("weight gradient of a two-source conv with padded channels")
     b.plan.pgrads.append(dict(kind="conv", key=t["key"], nin=t["nin"], gw=gw, gb=gb, scale=scale, cout=t["cout"],
-                              cin=cin_true, cin_s=cin_s, k=k))
+                              cin=cin_true, cin_s=cin_s, k=k, kout=kout))
 
 
 def _temb_param_grads(b):

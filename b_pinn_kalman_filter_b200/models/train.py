@@ -197,7 +197,7 @@ class Trainer:
         out = []
         if g["kind"] == "conv":
             k, cs = g["k"], g["cin_s"]
-            gw = g["gw"].to(torch.float32).view(-1, k, k, cs) * g["scale"]
+            gw = g["gw"][:, :g["kout"]].to(torch.float32).reshape(-1, k, k, cs) * g["scale"]
             gb = g["gb"]
             if g["nin"] == "qkv":
                 C = g["cout"] // 3
