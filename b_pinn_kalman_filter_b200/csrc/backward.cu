@@ -440,6 +440,10 @@ extern "C" int b200_attention_bwd(const void* qkv, const void* dout, void* dqkv,
                                   int C, float scale, cudaStream_t st) {
   if (!qkv || !dout || !dqkv || !scratch || B < 0 || L <= 0 || C <= 0 || C % 8) return B200_ERR_ARG;
   if (B == 0) return B200_OK;
+  // bf16, L = C = 256 (every shipped network's attention): tensor-core path (attn_bwd_mma.cu); B200_ATTN_BWD_MMA=0: A/B
+  static const bool mma_on = [] { const char* e = getenv("B200_ATTN_BWD_MMA"); return !(e && e[0] == '0'); }();
+  if (mma_on && dtype == B200_DT_BF16 && b200_attention_bwd_mma_supported(L, C))
+    return b200_attention_bwd_mma(qkv, dout, dqkv, scratch, B, L, C, scale, st);
   float* P = scratch;
   float* dS = scratch + (size_t)B * L * L;
   const int tiles = (L + AB_ROWS - 1) / AB_ROWS;

@@ -256,6 +256,10 @@ int b200_rk_stage(float* x32_out, double* y_out, const double* y, const float* K
 int b200_rk_error(double* partial, const double* y, const double* y_new, const float* K, long long kstride, int ns,
                   const double* e_host, double h, double atol, double rtol, long long n, cudaStream_t stream);
 
+/* attention backward on tensor cores (bf16, L = C = 256; warp-level MMA): what b200_attention_bwd dispatches to */
+int b200_attention_bwd_mma_supported(int L, int C);
+int b200_attention_bwd_mma(const void* qkv, const void* dout, void* dqkv, void* scratch, int B, int L, int C, float scale,
+                           cudaStream_t stream);
 /* ---- training step (losses.py:165-222 step_fn: loss.backward(); optimize_fn = warm-up + clip_grad_norm_ + Adam,
  * losses.py:48-66; models/ema.py:36-56) -------------------------------------------------------------------------------
  * Weight gradients are contracted by b200_conv2d_tc / b200_conv2d_simt over K = pixels: b200_transpose2d gives dY^T

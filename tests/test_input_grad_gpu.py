@@ -126,3 +126,32 @@ def test_likelihood_rhs_matches_oracle(cuda, precision, tol):
     drift, div = likelihood.get_drift_div_fn(sde)(m, x.to(cuda), t.to(cuda), eps.to(cuda))
     assert cases.rel_l2(drift.cpu(), ref_drift) < tol
     assert cases.rel_l2(div.cpu(), ref_div) < 5 * tol, (div.cpu(), ref_div)
+
+
+@pytest.mark.parametrize("B", [1, 5])
+def test_attention_backward_tensor_core_path(cuda, B):
+    """b200_attention_bwd in bf16 at L = C = 256 (warp-MMA kernels, csrc/attn_bwd_mma.cu) against torch autograd in fp32
+    on the same bf16-rounded operands."""
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import backward  # noqa: F401  (registers the signature)
+    L = C = 256
+    g = torch.Generator().manual_seed(B)
+    qkv = torch.randn(B, L, 3 * C, generator=g)
+    qkv[:, :, :C] *= 1.5
+    qkv = qkv.to(cuda, torch.bfloat16)
+    dout = torch.randn(B, L, C, generator=g).to(cuda, torch.bfloat16)
+    lib = _lib.lib()
+    assert lib.b200_attention_bwd_mma_supported(L, C) == 1
+    dqkv = torch.full((B, L, 3 * C), float("nan"), device=cuda, dtype=torch.bfloat16)
+    scratch = torch.empty(2 * B * L * L, device=cuda)
+    _lib.check(lib.b200_attention_bwd(_lib.ptr(qkv), _lib.ptr(dout), _lib.ptr(dqkv), _lib.ptr(scratch), 1, B, L, C,
+                                      C ** -0.5, _lib.stream()), "b200_attention_bwd")
+    torch.cuda.synchronize()
+    x = qkv.float().requires_grad_(True)
+    q, k, v = x.split(C, dim=-1)
+    o = torch.softmax(q @ k.transpose(1, 2) * C ** -0.5, dim=-1) @ v
+    ref, = torch.autograd.grad(o, x, dout.float())
+    assert torch.isfinite(dqkv.float()).all()
+    for name, sl in (("dq", slice(0, C)), ("dk", slice(C, 2 * C)), ("dv", slice(2 * C, 3 * C))):
+        err = cases.rel_l2(dqkv[..., sl].float().cpu(), ref[..., sl].cpu())
+        assert err < 1.5e-2, (name, err)
