@@ -86,8 +86,14 @@ __device__ __forceinline__ uint32_t mapa_cta(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
+// Arrive on a barrier of another CTA of the cluster.  Default semantics (.release at CTA scope), as CUTLASS's
+// ClusterBarrier::arrive: `.release.cluster` compiles to MEMBAR.ALL.GPU + ERRBAR in front of the arrive (ncu source page,
+// profiles/r02f: 29 % of the GroupNorm transform warps' time, and one per epilogue warp and tile in every pair variant).
+// What crosses CTAs here never needs it: TMEM hand-offs are ordered by tcgen05.fence::before/after_thread_sync, and the
+// transform warps' shared-memory writes are read by the tensor core of their OWN SM (made visible to the async proxy by
+// fence.proxy.async before the arrive).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 __device__ __forceinline__ void tma_load_4d_2sm(uint32_t dst, const CUtensorMap* map, uint32_t bar_cluster, int c0,
                                                 int c1, int c2, int c3) {

@@ -1,6 +1,7 @@
 """Summaries of the two ncu passes of /opt/skills/guides/B200_PROFILING.md (run here, no GPU needed):
     python profiles/summarize_ncu.py launches gpurun_out/r01f_launches.csv "<command line>"  > profiles/..._summary.txt
     python profiles/summarize_ncu.py full gpurun_out/r01f_conv_tc_full.ncu-rep               > profiles/..._ncu_full.txt
+    python profiles/summarize_ncu.py dram gpurun_out/r02f_conv_tc_dram.csv "<what>" profiles/conv_tc_traffic.json > ..._dram_summary.txt
 `full` also writes <rep stem>_traffic.json: per-launch average DRAM bytes of the captured kernel (bench.py's
 roofline.traffic reads profiles/conv_tc_traffic.json)."""
 import csv
@@ -87,8 +88,50 @@ def full(rep):
         json.dump(traffic, f)
 
 
+def dram(path, cmd, out_json):
+    """per-variant sums of the dram / L2 / tensor-pipe pass over every conv_tc launch of one forward (csv log of
+    `ncu --metrics dram__bytes_read.sum,... -k regex:conv_tc_kernel`); writes the traffic json bench.py reads"""
+    with open(path, newline="") as f:
+        lines = [ln for ln in f if not ln.startswith("==")]
+    per_id = OrderedDict()
+    for r in csv.DictReader(io.StringIO("".join(lines))):
+        d = per_id.setdefault(r["ID"], {"k": r["Kernel Name"].split("(")[0]})
+        v = float(r["Metric Value"].replace(",", ""))
+        m, u = r["Metric Name"], r.get("Metric Unit", "")
+        if m.startswith("dram__bytes") or m.startswith("lts__t_bytes"):
+            v = to_bytes(v, u[:1] if u.lower() not in ("byte", "bytes") else "")
+        elif m == "gpu__time_duration.sum":
+            ul = u.lower()
+            v = v * (1e-3 if ul.startswith("n") else 1.0 if ul.startswith("u") else 1e3)
+        d[m] = v
+    agg = OrderedDict()
+    for d in per_id.values():
+        a = agg.setdefault(d["k"], {"n": 0, "t": 0.0, "r": 0.0, "w": 0.0, "l2": 0.0, "tp": 0.0})
+        t = d.get("gpu__time_duration.sum", 0.0)
+        a["n"] += 1; a["t"] += t; a["r"] += d.get("dram__bytes_read.sum", 0.0); a["w"] += d.get("dram__bytes_write.sum", 0.0)
+        a["l2"] += d.get("lts__t_bytes.sum", 0.0)
+        a["tp"] += t * d.get("sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", 0.0)
+    n = sum(a["n"] for a in agg.values()); t = sum(a["t"] for a in agg.values())
+    r = sum(a["r"] for a in agg.values()); w = sum(a["w"] for a in agg.values())
+    print("# %s" % cmd)
+    print("# template arguments: <BN, EPI, HALO, DS, PAIR, GNF>")
+    print("# %d launches, %.1f us total, DRAM read %.1f MB + write %.1f MB = %.2f MB per launch, L2 traffic %.1f MB, "
+          "tensor pipe active %.1f%% (time-weighted over all launches)" %
+          (n, t, r / 1e6, w / 1e6, (r + w) / max(n, 1) / 1e6, sum(a["l2"] for a in agg.values()) / 1e6,
+           sum(a["tp"] for a in agg.values()) / max(t, 1e-9)))
+    for k, a in sorted(agg.items(), key=lambda kv: -kv[1]["t"]):
+        print("%-46s n=%3d %9.1f us  dram r %8.1f MB w %8.1f MB  L2 %9.1f MB  tensor pipe active %.1f%% (time-weighted)" %
+              (k, a["n"], a["t"], a["r"] / 1e6, a["w"] / 1e6, a["l2"] / 1e6, a["tp"] / max(a["t"], 1e-9)))
+    if out_json:
+        with open(out_json, "w") as f:
+            json.dump({"launches": n, "dram_bytes_read": r, "dram_bytes_write": w, "dram_bytes_per_launch": (r + w) / max(n, 1),
+                       "source": cmd}, f)
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "")
+    elif sys.argv[1] == "dram":
+        dram(sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else "", sys.argv[4] if len(sys.argv) > 4 else None)
     else:
         full(sys.argv[2])
