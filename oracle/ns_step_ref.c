@@ -9,8 +9,11 @@
  *                                                             (op/ns_step_kernel.cu:30-47, 248-254)
  * The reference only indexes correctly when H == W; this oracle requires H == W.
  * Expression types (float vs double literal promotion) follow the reference statement by statement.
- * PARITY: pinned against the reference's own CUDA extension on the GPU box when oracle/_ref/ was built
- * (tests/test_ns_step.py::test_vs_reference_extension); otherwise unpinned.
+ * PARITY: pinned on the GPU box against the reference's own CUDA extension, built unmodified from
+ * /root/reference/op/ns_step{.cpp,_kernel.cu} into oracle/_ref/ns_step_forward by oracle/build_ref_ext.py:
+ * tests/test_ref_ext_gpu.py compares this file (and the product kernels) with update_density / update_velocity /
+ * update_pressure at B = 1 for four grid sizes, with the B = 3 bug-compatible composition, and over a rollout.
+ * Those tests FAIL (not skip) when CUDA is present and oracle/_ref is missing.
  *
  * Build: make -C oracle   (gcc -O2 -fopenmp -ffp-contract=off -shared)
  */
