@@ -928,10 +928,12 @@ int launch_pair(const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap&
   cfg.gridDim = dim3(2 * clusters); cfg.blockDim = dim3(TC_THREADS + (HALO ? 32 : 0) + (GNF ? 32 * TC_XF_WARPS : 0));
   cfg.dynamicSmemBytes = SP::TOTAL;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;       // see b200_launch_pdl (common.cuh)
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = b200_pdl_enabled() ? 2 : 1;
   cudaError_t le = cudaLaunchKernelEx(&cfg, kern, a1, a2, w, om, rm, xm ? xm->x1 : a1, xm ? xm->x2 : a1, p);
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();

@@ -225,9 +225,13 @@ static int gn_threads(int C) {
 using namespace b200;
 
 extern "C" int b200_gn_nsplit(int B, int HW) {
-  // enough blocks to fill 148 SMs a few times over, but never fewer than 64 pixels per block
-  int want = (B200_NUM_SMS * 8 + B - 1) / (B > 0 ? B : 1);
-  int maxs = HW / 64 > 0 ? HW / 64 : 1;
+  // At most ONE wave of blocks (gn_apply_kernel<bf16>: 64 registers x 256 threads = 4 blocks per SM), never fewer than
+  // 128 pixels per block: every block folds the image's statistics before it streams (up to 16 slots x C x 8 B), so
+  // more, smaller blocks are slower, not faster -- measured inside a CUDA graph (profiles/prof_gn.py, NS_LIST): 128
+  // images of 32x32x128: 23.9 us with 10 splits (the old "8 blocks per SM, several waves" rule), 11.4 us = 5.9 TB/s
+  // with 4; 1024 images: 102.9 us with 2 splits, 98.0 us with 1.
+  int want = (B200_NUM_SMS * 4) / (B > 0 ? B : 1);
+  int maxs = HW / 128 > 0 ? HW / 128 : 1;
   int s = want < maxs ? want : maxs;
   if (s < 1) s = 1;
   if (s > 32) s = 32;

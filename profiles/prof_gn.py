@@ -37,3 +37,21 @@ ms = t(lambda: lib.b200_gn_apply(P(x), C, None, 0, 1, B, HW, G, ns, P(part), P(g
 print("gn_apply (partials): %.3f ms  %.0f GB/s" % (ms, nbytes / ms / 1e6))
 ms = t(lambda: out.copy_(x))
 print("torch copy: %.3f ms  %.0f GB/s" % (ms, nbytes / ms / 1e6))
+# the same launch 40 times inside a CUDA graph (what the PC loop pays: no host launch cost), for each NS in NS_LIST
+def graph_us(fn, n=40):
+    s2 = torch.cuda.Stream()
+    with torch.cuda.stream(s2):
+        st2 = _lib.stream()
+        fn(st2); s2.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s2):
+            for _ in range(n): fn(_lib.stream())
+        for _ in range(3): g.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(s2)
+        for _ in range(5): g.replay()
+        e1.record(s2); s2.synchronize()
+    return e0.elapsed_time(e1) / 5 / n * 1e3
+for nsv in [int(v) for v in os.environ.get("NS_LIST", str(ns)).split(",")]:
+    us = graph_us(lambda st_: lib.b200_gn_apply_stats(P(x), C, P(st), T, None, 0, None, 0, 1, B, HW, G, nsv, P(gamma), P(beta), 1e-6, 1, P(out), st_))
+    print("graph: gn_apply_stats B=%d HW=%d C=%d ns=%d: %.2f us  %.0f GB/s" % (B, HW, C, nsv, us, nbytes / us / 1e3))
