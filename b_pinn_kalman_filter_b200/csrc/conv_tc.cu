@@ -966,10 +966,10 @@ bool ds_enabled() {
 
 namespace b200 {
 int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides,
-                  const uint32_t* box, int l2_256, const uint32_t* estr) {
+                  const uint32_t* box, int l2_256, const uint32_t* estr, int f32) {
   MapKey key;
   for (int i = 0; i < 14; ++i) key.v[i] = 0;
-  key.v[0] = (uint64_t)ptr; key.v[1] = (uint64_t)rank | ((uint64_t)l2_256 << 8);
+  key.v[0] = (uint64_t)ptr; key.v[1] = (uint64_t)rank | ((uint64_t)l2_256 << 8) | ((uint64_t)(f32 ? 1 : 0) << 12);
   if (estr) for (int i = 0; i < rank; ++i) key.v[1] |= (uint64_t)estr[i] << (16 + 8 * i);
   for (int i = 0; i < rank; ++i) { key.v[2 + i] = dims[i]; key.v[6 + i] = box[i]; }
   for (int i = 0; i + 1 < rank; ++i) key.v[10 + i] = strides[i];
@@ -984,7 +984,7 @@ int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* d
   cuuint32_t bx[4], es[4] = {1, 1, 1, 1};
   for (int i = 0; i < rank; ++i) { d[i] = dims[i]; bx[i] = box[i]; if (estr) es[i] = estr[i]; }
   for (int i = 0; i + 1 < rank; ++i) st[i] = strides[i];
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es,
+  CUresult r = enc(out, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(ptr), d, st, bx, es,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    l2_256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

@@ -169,9 +169,10 @@ __device__ __forceinline__ void tma_store_4d(uint32_t src, const CUtensorMap* ma
 // generic-proxy writes to shared memory -> visible to the async proxy (UMMA / TMA reads)
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// Cached cuTensorMapEncodeTiled (bf16, 128B swizzle, zero OOB fill); rank <= 4, strides in bytes for dims 1..rank-1.
-// Returns B200_OK / B200_ERR_DRIVER.  Descriptors depend only on (pointer, extents, box), so they are memoised.
+// Cached cuTensorMapEncodeTiled (bf16, or fp32 with f32 = 1; 128B swizzle, zero OOB fill); rank <= 4, strides in bytes
+// for dims 1..rank-1.  Returns B200_OK / B200_ERR_DRIVER.  Descriptors depend only on (pointer, extents, box, type), so
+// they are memoised.
 int tc_tensor_map(CUtensorMap* out, const void* ptr, int rank, const uint64_t* dims, const uint64_t* strides,
-                  const uint32_t* box, int l2_256, const uint32_t* elem_strides = nullptr);
+                  const uint32_t* box, int l2_256, const uint32_t* elem_strides = nullptr, int f32 = 0);
 
 }  // namespace b200

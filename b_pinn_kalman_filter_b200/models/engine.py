@@ -435,8 +435,17 @@ class ScoreEngine:
         self.net_builder = net_builder
         self.device = torch.device(device)
         self.precision = precision
-        self.dt = {"bf16": DT_BF16, "fp32": DT_F32}[precision]
+        # "bf16": tensor-core mode (bf16 operands, fp32 accumulate).  "fp32": strict mode -- fp32 activations and weights;
+        # convolutions on the tensor cores through the three-term tf32 split with grouped fp32 accumulation
+        # (csrc/conv_tc32.cu: as close to the exact convolution as cuDNN's fp32 kernels), everything else on CUDA cores.
+        # "tf32": the same with the single tf32 product (what cudnn.allow_tf32 gives the reference).  "fp32_simt": strict
+        # mode with every convolution on CUDA cores (the reference point the split is tested against; B200_TC32=0).
+        self.dt = {"bf16": DT_BF16, "fp32": DT_F32, "tf32": DT_F32, "fp32_simt": DT_F32}[precision]
         self.use_tc = bool(use_tensor_cores) and self.dt == DT_BF16
+        self.tc32_terms = {"fp32": 3, "tf32": 1}.get(precision, 0) if bool(use_tensor_cores) else 0
+        if os.environ.get("B200_TC32", "1") == "0":
+            self.tc32_terms = 0
+        self.tc32_convs = 0
         self.fuse_gn_stats = True           # GroupNorm statistics as a by-product of the producing conv's epilogue
         # GroupNorm + SiLU applied inside the consuming conv's operand pipeline: True = where it is the faster form
         # (b200_conv2d_tc_gn_preferred), "all" = wherever the fused kernel can run, False = never
@@ -449,6 +458,7 @@ class ScoreEngine:
         self.workspace = Workspace(self.device)
         self.params = {}           # reference-layout fp32 tensors on device
         self._packed = {}
+        self._splits = {}          # packed fp32 weight (by address) -> (w, tf32 high part, low part): strict-mode tensor cores
         self._recipes = {}         # cache key -> (method name, args): how to rebuild a packed tensor (refresh_packed)
         self.train_dropout, self.train_seed, self.train_step, self.dropout_layers = 0.0, 0, None, 0
         self._dev = {}
@@ -544,6 +554,22 @@ class ScoreEngine:
             self._recipes[pk] = ("packed_conv", (key, nin, cin_store, cout_store))
         return self._packed[pk]
 
+    def split_tf32(self, w):
+        """(tf32(w), w - tf32(w)) of a packed fp32 weight tensor: the operands of b200_conv2d_tc32 (cached per tensor;
+        `refresh_packed` recomputes them after the parameters have changed in place)."""
+        ent = self._splits.get(w.data_ptr())
+        if ent is None:
+            ent = (w, torch.empty_like(w), torch.empty_like(w))
+            self._splits[w.data_ptr()] = ent
+            self._run_split(ent)
+        return ent[1], ent[2]
+
+    @staticmethod
+    def _run_split(ent):
+        w, hi, lo = ent
+        _lib.check(_lib.lib().b200_split_tf32(_lib.ptr(w), _lib.ptr(hi), _lib.ptr(lo), w.numel(), _lib.stream()),
+                   "b200_split_tf32")
+
     def packed_conv_sc(self, key1, key2, nin2, cin, cx, cout):
         """[W1 | W2]: [Cout][9 cin + cx] in the activation dtype (K contiguous) and the summed bias b1 + b2 (fp32)."""
         pk = (key1, key2, "sc")
@@ -570,6 +596,8 @@ class ScoreEngine:
             for o, n in zip(old if isinstance(old, tuple) else (old,), new if isinstance(new, tuple) else (new,)):
                 o.copy_(n)
             self._packed[pk] = old
+        for ent in self._splits.values():
+            self._run_split(ent)
 
     def packed_bias(self, key, nin, cout_store):
         pk = (key, "bias", cout_store)
@@ -603,6 +631,12 @@ class ScoreEngine:
         if self.use_tc and tc.conv_supported(b, x, x2, out, ksize, stride, tuple(pad)):
             tc.emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, self.conv_flops(b, x, x2, out, ksize))
             self.tc_convs += 1
+            return
+        if self.tc32_terms and self.dt == DT_F32 and tc.conv32_supported(b, x, x2, out, ksize, stride, tuple(pad)):
+            hi, lo = self.split_tf32(w)
+            tc.emit_conv32(b, x, x2, hi, lo, bias, temb_ptr, res, out_scale, out, ksize, self.tc32_terms,
+                           self.conv_flops(b, x, x2, out, ksize))
+            self.tc32_convs += 1
             return
         self.simt_convs += 1
         p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)

@@ -1,6 +1,6 @@
 """Tensor-core (tcgen05 / TMEM / TMA) launch selection for the score engine.  See csrc/conv_tc.cu."""
 from .. import _lib
-from .._lib import c_float, c_int, c_vp
+from .._lib import c_float, c_int, c_ll, c_vp
 
 _lib.register_signature("b200_conv2d_tc_supported", [c_int] * 9)
 _lib.register_signature("b200_conv2d_tc", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_vp,
@@ -25,6 +25,11 @@ _lib.register_signature("b200_conv2d_tc_gn", [c_vp, c_int, c_vp, c_int, c_vp, c_
 _lib.register_signature("b200_conv2d_tc_sc", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp,
                                               c_int, c_float, c_vp, c_vp, c_int, c_int, c_int, c_int])
 
+_lib.register_signature("b200_split_tf32", [c_vp, c_vp, c_vp, c_ll, c_vp])
+_lib.register_signature("b200_conv2d_tc32_supported", [c_int] * 7)
+_lib.register_signature("b200_conv2d_tc32", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_vp]
+                        + [c_int] * 6 + [c_vp])
+
 ENABLED = True
 FUSE_SHORTCUT = True  # Conv_2 (1x1 shortcut) folded into Conv_1's K loop (b200_conv2d_tc_sc)
 FUSE_GN = True        # GroupNorm + SiLU inside the consumer conv's operand pipeline (b200_conv2d_tc_gn)
@@ -43,6 +48,21 @@ def emit_conv(b, x, x2, w, bias, temb_ptr, res, out_scale, out, ksize, flops):
            out, 0, None, None, b.B, x.H, x.W, out.C, ksize, flops=flops,
            tag="%dx%d %dx%d %d->%d" % (ksize, ksize, x.H, x.W, x.C + c2, out.C))
     out.producer = (len(b.plan.ops) - 1, 13)      # (launch index, position of the `stats` argument)
+
+
+def conv32_supported(b, x, x2, out, ksize, stride, pad):
+    """Strict-mode (fp32) convolution on the tensor cores: b200_conv2d_tc32."""
+    if not ENABLED or stride != 1 or pad != (ksize // 2, ksize // 2) or (out.H, out.W) != (x.H, x.W):
+        return False
+    c2 = x2.C if x2 is not None else 0
+    return bool(_lib.lib().b200_conv2d_tc32_supported(x.C, c2, b.B, x.H, x.W, out.C, ksize))
+
+
+def emit_conv32(b, x, x2, w_hi, w_lo, bias, temb_ptr, res, out_scale, out, ksize, terms, flops):
+    p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
+    b.emit("b200_conv2d_tc32", x, x.C, p2, c2, w_hi.data_ptr(), w_lo.data_ptr(), bias.data_ptr(), temb_ptr, b.temb_stride,
+           res, out_scale, out, b.B, x.H, x.W, out.C, ksize, terms, flops=flops,
+           tag="%dx%d %dx%d %d->%d tf32x%d" % (ksize, ksize, x.H, x.W, x.C + c2, out.C, terms))
 
 
 def conv_gn_supported(b, x1, x2, out, ksize, stride, pad):

@@ -140,6 +140,17 @@ int b200_linear_f32(const float* x, const float* W, const float* bias, float* ou
                     int act_out, cudaStream_t stream);
 int b200_add_scale(const void* a, const void* b, void* out, int dtype, long long n, float s, cudaStream_t stream);
 int b200_nearest_up2_nhwc(const void* x, void* out, int dtype, int B, int H, int W, int C, cudaStream_t stream);
+/* Strict-mode convolution on the tensor cores: fp32 NHWC activations, fp32 weights [Cout][kh][kw][Cin] pre-split into
+ * (w_hi, w_lo) = (tf32(w), w - tf32(w)) by b200_split_tf32; tcgen05.mma kind::tf32, three-term split x w ~= xh wh +
+ * xl wh + xh wl with fp32 accumulation (terms = 3: fp32-faithful, for `precision="fp32"`), or xh wh only (terms = 1: plain
+ * TF32, what cudnn.allow_tf32 gives the reference).  out = ((conv + bias[n] + temb[b,n]) + res) * out_scale, fp32 NHWC.
+ * replaces nn.Conv2d 3x3 / 1x1 and NIN in fp32 (models/layers.py:96-118, 537-546).  C1 % 32 == C2 % 32 == 0,
+ * Cout % 128 == 0, ksize 1 or 3 (stride 1, pad ksize / 2). */
+int b200_split_tf32(const float* w, float* hi, float* lo, long long n, cudaStream_t stream);
+int b200_conv2d_tc32_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize);
+int b200_conv2d_tc32(const float* x1, int C1, const float* x2, int C2, const float* w_hi, const float* w_lo,
+                     const float* bias, const float* temb, int temb_stride, const float* res, float out_scale,
+                     float* out, int B, int H, int W, int Cout, int ksize, int terms, cudaStream_t stream);
 /* implicit-GEMM convolution on CUDA cores (strict fp32 path + odd shapes); epilogue
  * out = ((conv + bias[n] + temb[b,n]) + res) * out_scale.  replaces nn.Conv2d / NIN (models/layers.py:96-118,537-546) */
 int b200_conv2d_simt(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,
