@@ -397,6 +397,25 @@ def other_config_measurements(dev, timeit):
     plan = m.engine.plan(B, grad=True)
     res["C4_dps_rhs_forward_plus_input_grad"] = {"batch": B, "ms": ms, "rhs_evals_per_s": B / ms * 1e3,
                                                  "launches": len(plan.ops), "finite": bool(torch.isfinite(rhs()).all())}
+    del m, plan
+    # the precision modes of the C3 score network (north_star: "TF32/bf16 conv modes"), one forward at 128 images:
+    # bf16 = the headline's mode; tf32 / fp32 = fp32 activations with the convolutions on tcgen05 kind::tf32 (one product /
+    # the fp32-faithful three-term split); fp32_simt = the CUDA-core strict mode the split replaced
+    modes = {}
+    for precision in ("bf16", "tf32", "fp32", "fp32_simt"):
+        cfg = configs.get_config(CONFIG)
+        cfg.device = dev
+        m = mutils.ScoreModel(cfg, device=dev, precision=precision, init=False)
+        m.init_weights(42, zero_init_scale=1.0)
+        plan = m.engine.plan(128)
+        plan.x_in.normal_()
+        plan.labels.fill_(1.0)
+        ms = timeit(lambda: plan.run(_lib.stream()), iters=3)
+        modes[precision] = {"ms_per_forward": ms, "tflops": plan.flops() / ms / 1e9,
+                            "convs_tcgen05": m.engine.tc_convs + m.engine.tc32_convs, "convs_cuda_cores": m.engine.simt_convs,
+                            "finite": bool(torch.isfinite(plan.out).all())}
+        del m, plan
+    res["C3_precision_modes_forward_b128"] = modes
     return res
 
 

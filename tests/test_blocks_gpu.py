@@ -62,7 +62,10 @@ def test_groupnorm_silu(cuda, dtype, B, HW, C1, C2, G):
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("B,H,W,C,up,down,pad", [(2, 32, 32, 128, 1, 2, (1, 1)), (2, 4, 4, 256, 2, 1, (2, 1)),
                                                 (3, 16, 16, 256, 2, 1, (2, 1)), (2, 32, 32, 8, 1, 1, (2, 2)),
-                                                (2, 8, 8, 256, 1, 1, (2, 2)), (1, 64, 64, 128, 1, 2, (1, 1))])
+                                                (2, 8, 8, 256, 1, 1, (2, 2)), (1, 64, 64, 128, 1, 2, (1, 1)),
+                                                # more up-2 shapes: one block row, ragged extents, C = 64
+                                                (2, 8, 8, 128, 2, 1, (2, 1)), (2, 20, 20, 64, 2, 1, (2, 1)),
+                                                (1, 128, 128, 64, 2, 1, (2, 1))])
 def test_upfirdn2d_nhwc(cuda, dtype, B, H, W, C, up, down, pad):
     L = _lib()
     rng = np.random.default_rng(H + C)
