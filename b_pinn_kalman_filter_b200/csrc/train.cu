@@ -296,12 +296,30 @@ __global__ void __launch_bounds__(256) dropout_kernel(T* __restrict__ y, const T
 // (losses.py:48-66 -> torch.optim.Adam; models/ema.py:36-56).  hyper (device, refreshed by the host each step):
 //   [0] lr  [1] beta1  [2] beta2  [3] eps  [4] weight_decay  [5] 1 - beta1^t  [6] 1 - beta2^t  [7] max_norm (< 0: off)
 //   [8] 1 - ema_decay_t      sumsq[0] = sum of squares of the (already all-reduced) gradient.
+// Block partials land in a per-device scratch array and the LAST block to finish adds them in index order: the same bits
+// every run (a float atomicAdd per block made the clip factor, and with it every parameter, depend on block timing).
+// One array per device: calls on different streams of one device must not overlap (one training stream per device).
+constexpr int SUMSQ_MAX_BLOCKS = 148 * 16;
+__device__ float g_sumsq_part[SUMSQ_MAX_BLOCKS];
+__device__ unsigned int g_sumsq_done;
 __global__ void __launch_bounds__(256) sumsq_f32_kernel(float* __restrict__ out, const float* __restrict__ g, long long n) {
   __shared__ float red[32];
+  __shared__ bool last;
   float a = 0.0f;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) a = fmaf(g[i], g[i], a);
   a = block_sum(a, red);
-  if (threadIdx.x == 0) atomicAdd(out, a);
+  if (threadIdx.x == 0) {
+    g_sumsq_part[blockIdx.x] = a;
+    __threadfence();
+    last = atomicAdd(&g_sumsq_done, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  float t = 0.0f;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) t += __ldcg(&g_sumsq_part[i]);   // fixed assignment and order
+  t = block_sum(t, red);
+  if (threadIdx.x == 0) { out[0] = t; g_sumsq_done = 0u; }
 }
 
 __global__ void __launch_bounds__(256) adam_ema_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
@@ -443,12 +461,10 @@ extern "C" int b200_dropout(void* y, const void* x, int dtype, long long n, floa
   B200_RETURN_LAST();
 }
 
-// sumsq[0] = sum g^2 (zeroed first)
+// sumsq[0] = sum g^2, bit-reproducible
 extern "C" int b200_grad_sumsq(float* sumsq, const float* g, long long n, cudaStream_t st) {
   if (!sumsq || !g || n <= 0) return B200_ERR_ARG;
-  cudaError_t e = cudaMemsetAsync(sumsq, 0, sizeof(float), st);
-  if (e != cudaSuccess) return -(1000 + (int)e);
-  sumsq_f32_kernel<<<tr_grid(n), 256, 0, st>>>(sumsq, g, n);
+  sumsq_f32_kernel<<<tr_grid(n), 256, 0, st>>>(sumsq, g, n);          // tr_grid <= SUMSQ_MAX_BLOCKS
   B200_RETURN_LAST();
 }
 
@@ -458,5 +474,58 @@ extern "C" int b200_adam_ema(float* p, float* m, float* v, float* ema, const flo
                              const float* sumsq, float grad_scale, long long n, cudaStream_t st) {
   if (!p || !m || !v || !g || !hyper || !sumsq || n <= 0) return B200_ERR_ARG;
   adam_ema_kernel<<<tr_grid(n), 256, 0, st>>>(p, m, v, ema, g, hyper, sumsq, grad_scale, n);
+  B200_RETURN_LAST();
+}
+
+// ---- batched strided copy --------------------------------------------------------------------------------------------
+// After every optimizer step the plans' derived weight copies have to follow the flat fp32 parameters: forward weights
+// re-packed to [Cout][kh][kw][Cin] bf16 (NIN transposed, q/k/v and the 1x1 shortcuts stacked), backward-data weights
+// flipped and transposed, and before it the per-layer weight gradients scattered from their GEMM layouts into the flat
+// gradient buffer.  As ~1500 torch copy / permute / cast calls that was 20 of the 76 ms of a C3 training step, all of it
+// host time.  Each of those is a <= 4-D strided copy with a scale and a type change: the host writes them ONCE into a
+// descriptor table (models/copylist.py) and one launch executes the whole table.
+namespace b200 {
+struct CopyDesc {
+  const void* src; const void* src2; void* dst;        // dst[i] = scale * (src[j(i)] + src2[j(i)])   (src2 may be null)
+  long long ss[4], ds[4];                              // element strides of src (src2 alike) and dst, dimension 3 fastest
+  int n[4];                                            // extents
+  int flip;                                            // bit k: source index along dimension k runs backwards
+  float scale;
+  int sdt, ddt;                                        // B200_DT_F32 / B200_DT_BF16
+};
+constexpr int COPY_CHUNK = 2048;                       // elements per block
+
+__global__ void __launch_bounds__(256) copy_batch_kernel(const CopyDesc* __restrict__ descs, const int2* __restrict__ blocks) {
+  const int2 bk = blocks[blockIdx.x];                  // (descriptor, chunk)
+  const CopyDesc d = descs[bk.x];
+  const long long total = (long long)d.n[0] * d.n[1] * d.n[2] * d.n[3];
+  const long long e0 = (long long)bk.y * COPY_CHUNK;
+  const long long e1 = e0 + COPY_CHUNK < total ? e0 + COPY_CHUNK : total;
+  for (long long e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
+    long long r = e;
+    const int i3 = (int)(r % d.n[3]); r /= d.n[3];
+    const int i2 = (int)(r % d.n[2]); r /= d.n[2];
+    const int i1 = (int)(r % d.n[1]);
+    const int i0 = (int)(r / d.n[1]);
+    const int j0 = (d.flip & 1) ? d.n[0] - 1 - i0 : i0, j1 = (d.flip & 2) ? d.n[1] - 1 - i1 : i1;
+    const int j2 = (d.flip & 4) ? d.n[2] - 1 - i2 : i2, j3 = (d.flip & 8) ? d.n[3] - 1 - i3 : i3;
+    const long long so = j0 * d.ss[0] + j1 * d.ss[1] + j2 * d.ss[2] + j3 * d.ss[3];
+    const long long dof = i0 * d.ds[0] + i1 * d.ds[1] + i2 * d.ds[2] + i3 * d.ds[3];
+    float v = d.sdt == B200_DT_F32 ? ((const float*)d.src)[so] : __bfloat162float(((const bf16*)d.src)[so]);
+    if (d.src2) v += d.sdt == B200_DT_F32 ? ((const float*)d.src2)[so] : __bfloat162float(((const bf16*)d.src2)[so]);
+    v *= d.scale;
+    if (d.ddt == B200_DT_F32) ((float*)d.dst)[dof] = v; else ((bf16*)d.dst)[dof] = __float2bfloat16_rn(v);
+  }
+}
+}  // namespace b200
+
+extern "C" int b200_copy_desc_bytes(void) { return (int)sizeof(b200::CopyDesc); }
+extern "C" int b200_copy_chunk(void) { return b200::COPY_CHUNK; }
+// descs: device array of CopyDesc (layout above; b200_copy_desc_bytes each); blocks: device array of nblocks (descriptor,
+// chunk) int pairs covering every descriptor's ceil(elements / b200_copy_chunk()) chunks
+extern "C" int b200_copy_batch(const void* descs, const void* blocks, int nblocks, cudaStream_t st) {
+  if (!descs || !blocks || nblocks < 0) return B200_ERR_ARG;
+  if (nblocks == 0) return B200_OK;
+  b200::copy_batch_kernel<<<nblocks, 256, 0, st>>>((const b200::CopyDesc*)descs, (const int2*)blocks);
   B200_RETURN_LAST();
 }

@@ -11,6 +11,8 @@ kernel over the flat buffers; with a process group the flat gradient is all-redu
 """
 import math
 
+import os
+
 import torch
 
 from .. import _lib, sde_lib
@@ -195,47 +197,62 @@ class Trainer:
     def _targets(self, g):
         """[(key, tensor expression)] of one plan.pgrads entry."""
         out = []
+        # every entry is a VIEW of a gradient buffer the backward launches fill (plus a scale): the same list serves the
+        # descriptor table of _collect and, through .to() / mul, the torch form it replaced
         if g["kind"] == "conv":
-            k, cs = g["k"], g["cin_s"]
-            gw = g["gw"][:, :g["kout"]].to(torch.float32).reshape(-1, k, k, cs) * g["scale"]
+            k, cs, sc = g["k"], g["cin_s"], g["scale"]
+            gw = g["gw"][:, :g["kout"]].unflatten(1, (k, k, cs))
             gb = g["gb"]
             if g["nin"] == "qkv":
                 C = g["cout"] // 3
                 for i in range(3):
-                    out.append((g["key"] + ".NIN_%d.W" % i, gw[i * C:(i + 1) * C, 0, 0, :C].t()))
-                    out.append((g["key"] + ".NIN_%d.b" % i, gb[i * C:(i + 1) * C]))
+                    out.append((g["key"] + ".NIN_%d.W" % i, gw[i * C:(i + 1) * C, 0, 0, :C].t(), sc))
+                    out.append((g["key"] + ".NIN_%d.b" % i, gb[i * C:(i + 1) * C], 1.0))
             elif g["nin"]:
-                out.append((g["key"] + ".W", gw[:g["cout"], 0, 0, :g["cin"]].t()))
-                out.append((g["key"] + ".b", gb[:g["cout"]]))
+                out.append((g["key"] + ".W", gw[:g["cout"], 0, 0, :g["cin"]].t(), sc))
+                out.append((g["key"] + ".b", gb[:g["cout"]], 1.0))
             else:
-                out.append((g["key"] + ".weight", gw[:g["cout"], :, :, :g["cin"]].permute(0, 3, 1, 2)))
-                out.append((g["key"] + ".bias", gb[:g["cout"]]))
+                out.append((g["key"] + ".weight", gw[:g["cout"], :, :, :g["cin"]].permute(0, 3, 1, 2), sc))
+                out.append((g["key"] + ".bias", gb[:g["cout"]], 1.0))
         elif g["kind"] == "gn":
             buf = g["buf"].view(g["C"], 2)
-            out += [(g["key"] + ".weight", buf[:, 0]), (g["key"] + ".bias", buf[:, 1])]
+            out += [(g["key"] + ".weight", buf[:, 0], 1.0), (g["key"] + ".bias", buf[:, 1], 1.0)]
         elif g["kind"] == "dense":
             H4, row = self.plan.temb["hidden"], 0
             gw = g["gw"].view(-1, H4)
             for prefix, oc in self.eng.dense_layout:
-                out += [(prefix + ".weight", gw[row:row + oc]), (prefix + ".bias", g["gb"][row:row + oc])]
+                out += [(prefix + ".weight", gw[row:row + oc], 1.0), (prefix + ".bias", g["gb"][row:row + oc], 1.0)]
                 row += oc
         elif g["kind"] == "linear":
-            out += [(g["key"] + ".weight", g["gw"].view(g["shape"])), (g["key"] + ".bias", g["gb"])]
+            out += [(g["key"] + ".weight", g["gw"].view(g["shape"]), 1.0), (g["key"] + ".bias", g["gb"], 1.0)]
         return out
 
     def _check_coverage(self):
         seen = set()
         for g in self.plan.pgrads:
-            for key, _ in self._targets(g):
+            for key, _, _ in self._targets(g):
                 if key in seen:
                     raise RuntimeError("parameter %s receives two gradients" % key)
                 seen.add(key)
         return seen
 
     def _collect(self):
-        for g in self.plan.pgrads:
-            for key, val in self._targets(g):
-                self.gviews[key].copy_(val)
+        """Per-layer gradients (GEMM layouts, bf16 or fp32, padded) -> the flat fp32 gradient buffer in the reference's
+        parameter order: ONE b200_copy_batch launch over a descriptor table built at the first call (as ~330 torch
+        slice / permute / cast / copy calls this was 6.4 ms of host time per step; B200_FAST_REFRESH=0 keeps that form)."""
+        if os.environ.get("B200_FAST_REFRESH", "1") == "0":
+            for g in self.plan.pgrads:
+                for key, val, sc in self._targets(g):
+                    self.gviews[key].copy_(val.to(torch.float32) * sc if sc != 1.0 else val)
+            return
+        if getattr(self, "_collect_cl", None) is None:
+            from .copylist import CopyList
+            cl = CopyList(self.flat_g.device)
+            for g in self.plan.pgrads:
+                for key, val, sc in self._targets(g):
+                    cl.add(self.gviews[key], val.view(self.gviews[key].shape), scale=sc)
+            self._collect_cl = cl.finalize()
+        self._collect_cl.run()
 
     # ---- gradient all-reduce, optimizer, EMA ----------------------------------------------------------------------
     def allreduce_grads(self):

@@ -300,6 +300,13 @@ int b200_dropout(void* y, const void* x, int dtype, long long n, float p, uint64
 int b200_grad_sumsq(float* sumsq, const float* g, long long n, cudaStream_t stream);
 int b200_adam_ema(float* p, float* m, float* v, float* ema, const float* g, const float* hyper, const float* sumsq,
                   float grad_scale, long long n, cudaStream_t stream);
+/* One launch for a table of <= 4-D strided copies with scale and fp32 <-> bf16 conversion (dst[i] = scale * (src[j(i)] +
+ * src2[j(i)])): what keeps the plans' packed / flipped weight copies and the flat gradient buffer in step with the flat
+ * parameters after optimizer.step() (the reference re-reads its nn.Parameters in place; no counterpart).  Descriptor
+ * layout: csrc/train.cu CopyDesc; built by models/copylist.py. */
+int b200_copy_desc_bytes(void);
+int b200_copy_chunk(void);
+int b200_copy_batch(const void* descs, const void* blocks, int nblocks, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

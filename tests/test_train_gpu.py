@@ -186,3 +186,36 @@ def test_weight_gradient_on_the_tensor_core_conv(cuda, shape):
     ref = torch.nn.grad.conv2d_weight(xx, (Cout, Ct, k, k), gy.float().permute(0, 3, 1, 2), stride=stride, padding=pad)
     got = gw.float().view(Cout, k, k, Ct).permute(0, 3, 1, 2)
     assert cases.rel_l2(got.cpu(), ref.cpu()) < 4e-3, cases.rel_l2(got.cpu(), ref.cpu())
+
+
+@pytest.mark.parametrize("name,precision", [("ve_sde", "bf16"), ("vp_ddpm", "fp32")])
+def test_descriptor_table_refresh_equals_torch_refresh(cuda, name, precision):
+    """Gradient collection and the re-packing of every derived weight copy after optimizer.step() run as ONE
+    b200_copy_batch launch each (models/copylist.py); the torch slice / permute / cast form they replaced
+    (B200_FAST_REFRESH=0) must give the same bits: parameters, EMA and the next step's loss after three steps."""
+    import os
+    c = cases.train_case(name)
+    g = c["g"]
+    results = []
+    old = os.environ.get("B200_FAST_REFRESH")
+    try:
+        for mode in ("0", "1"):
+            os.environ["B200_FAST_REFRESH"] = mode
+            m, sde, state, step_fn = _setup(c, cuda, precision)
+            losses_ = []
+            for i in range(3):
+                batch, t, z = (torch.from_numpy(g[k][i]).to(cuda) for k in ("batch", "t", "z"))
+                losses_.append(float(step_fn(state, batch, t=t, z=z)))
+            results.append((losses_, [p.clone() for p in m.parameters()], [p.clone() for p in state["ema"].shadow_params]))
+            if mode == "1":
+                assert m.trainer._collect_cl is not None and len(m.trainer._collect_cl) > 100
+                assert m.engine._refresh_cl[0].nblocks > 100
+    finally:
+        if old is None:
+            os.environ.pop("B200_FAST_REFRESH", None)
+        else:
+            os.environ["B200_FAST_REFRESH"] = old
+    (l0, p0, e0), (l1, p1, e1) = results
+    assert l0 == l1, (l0, l1)
+    assert all(torch.equal(a, b) for a, b in zip(p0, p1))
+    assert all(torch.equal(a, b) for a, b in zip(e0, e1))
