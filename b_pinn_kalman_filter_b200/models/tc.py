@@ -15,6 +15,7 @@ _lib.register_signature("b200_conv2d_tc_stat_slots", [c_int] * 3)
 _lib.register_signature("b200_gn_apply_stats", [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int,
                                                 c_int, c_int, c_vp, c_vp, c_float, c_int, c_vp, c_vp])
 
+_lib.register_signature("b200_gn_fold_stats", [c_vp, c_vp, c_int, c_int, c_int, c_vp])
 _lib.register_signature("b200_gn_coef", [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_float,
                                         c_vp])
 _lib.register_signature("b200_conv2d_tc_gn_supported", [c_int] * 7)
@@ -150,13 +151,24 @@ def emit_s2(b, x, w, bias, res, out_scale, out, flops):
     out.producer = (len(b.plan.ops) - 1, 7)
 
 
+FOLD_SLOTS = 64       # images whose producer leaves at least this many statistics slots get them folded once (64x64 and up)
+
+
 def request_stats(b, act):
-    """Makes the tensor-core conv that produced `act` also write the GroupNorm statistics; returns (ptr, slots)."""
+    """Makes the tensor-core conv that produced `act` also write the GroupNorm statistics; returns (ptr, slots).
+    Large images: the slots are summed ONCE by b200_gn_fold_stats (emitted here, i.e. in front of the first consumer)
+    and every consumer sees one slot."""
     if act.stats is None:
         T = _lib.lib().b200_conv2d_tc_stat_slots(b.B, act.H, act.W)
         buf = b.f32(b.B * T * act.C * 2)
         idx, pos = act.producer
         fn, args, name = b.plan.ops[idx]
         b.plan.ops[idx] = (fn, args[:pos] + (buf.data_ptr(),) + args[pos + 1:], name)
-        act.stats = (buf.data_ptr(), T)
+        if T >= FOLD_SLOTS:
+            folded = b.f32(b.B * act.C * 2)
+            b.emit("b200_gn_fold_stats", buf.data_ptr(), folded.data_ptr(), b.B, T, act.C,
+                   tag="%dx%d %d slots %d" % (act.H, act.W, act.C, T))
+            act.stats = (folded.data_ptr(), 1)
+        else:
+            act.stats = (buf.data_ptr(), T)
     return act.stats

@@ -181,6 +181,9 @@ int b200_conv2d_tc_stat_slots(int B, int H, int W);
  * the 3x3 shapes b200_conv2d_tc_gn_supported accepts (the halo + CTA-pair tile variants: H % 16 == 0, W % 8 == 0). */
 int b200_gn_coef(const float* st1, int T1, int C1, const float* st2, int T2, int C2, int B, int HW, int G,
                  const float* gamma, const float* beta, float eps, float* coef, cudaStream_t stream);
+/* [B][T][C][2] -> [B][1][C][2]: the per-tile statistics slots of a producing convolution summed once, in a fixed order,
+ * for the GroupNorm consumers of large images (T = 256 / 1024 at 128x128 / 256x256) */
+int b200_gn_fold_stats(const float* stats, float* out, int B, int T, int C, cudaStream_t stream);
 int b200_conv2d_tc_gn_supported(int C1, int C2, int B, int H, int W, int Cout, int ksize);
 /* Conv_1 of a residual block with its 1x1 shortcut `Conv_2(x)` folded in (models/layerspp.py:266-274):
  * out = (conv3x3(h; W1) + conv1x1(cat(xs1, xs2); W2) + bias) * out_scale with bias = b1 + b2 and
