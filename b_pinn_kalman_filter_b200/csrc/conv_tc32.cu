@@ -42,6 +42,7 @@ struct Conv32Params {
   int TW, TH, TB, tiles_w, tiles_h, num_m, num_n;
   int terms;                                              // 3: split, 1: plain TF32
   int flush;                                              // K blocks per TMEM accumulation group
+  int w_batched;                                          // B operand per image: 3-D weight maps {K, N, B} (batched GEMM)
   const float* bias; const float* temb; int temb_stride; const float* res; float out_scale;
   float* out;
 };
@@ -121,8 +122,13 @@ conv_tc32_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constan
             mbar_expect_tx(full_bar(stage), bytes);
             if (c < p.C1) tma_load_4d(sa, &mapA1, full_bar(stage), c, w0 + s - p.pad, h0 + r - p.pad, b0);
             else tma_load_4d(sa, &mapA2, full_bar(stage), c - p.C1, w0 + s - p.pad, h0 + r - p.pad, b0);
-            tma_load_2d(sa + 2 * T32_TILE, &mapWh, full_bar(stage), tap * Ctot + c, nt * T32_BN);
-            if (split) tma_load_2d(sa + 3 * T32_TILE, &mapWl, full_bar(stage), tap * Ctot + c, nt * T32_BN);
+            if (p.w_batched) {
+              tma_load_3d(sa + 2 * T32_TILE, &mapWh, full_bar(stage), c, nt * T32_BN, b0);
+              if (split) tma_load_3d(sa + 3 * T32_TILE, &mapWl, full_bar(stage), c, nt * T32_BN, b0);
+            } else {
+              tma_load_2d(sa + 2 * T32_TILE, &mapWh, full_bar(stage), tap * Ctot + c, nt * T32_BN);
+              if (split) tma_load_2d(sa + 3 * T32_TILE, &mapWl, full_bar(stage), tap * Ctot + c, nt * T32_BN);
+            }
           }
           if (++stage == T32_STAGES) { stage = 0; phase ^= 1; }
         }
@@ -257,6 +263,58 @@ conv_tc32_kernel(const __grid_constant__ CUtensorMap mapA1, const __grid_constan
   }
 }
 
+// rows of n fp32 values -> softmax in place; one warp per row (the scores of the strict-mode attention)
+__global__ void __launch_bounds__(256) softmax_rows_kernel(float* __restrict__ x, long long rows, int n) {
+  const long long r = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int lane = threadIdx.x & 31;
+  float* row = x + r * n;
+  float mx = -INFINITY;
+  for (int j = lane; j < n; j += 32) mx = fmaxf(mx, row[j]);
+  for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float den = 0.f;
+  for (int j = lane; j < n; j += 32) { const float e = expf(row[j] - mx); row[j] = e; den += e; }
+  for (int o = 16; o; o >>= 1) den += __shfl_xor_sync(0xffffffffu, den, o);
+  const float inv = 1.0f / den;
+  for (int j = lane; j < n; j += 32) row[j] *= inv;
+}
+
+// Operands of the strict-mode attention from the fused projection qkv [B][L][3C]: k split into (hi, lo) as dense [B][L][C],
+// v transposed to [B][C][L] (the K-major B operand of p v) and split.  One 32 x 32 tile per block (256 threads).
+__global__ void __launch_bounds__(256) attn32_prep_kernel(const float* __restrict__ qkv, float* __restrict__ k_hi,
+                                                          float* __restrict__ k_lo, float* __restrict__ vt_hi,
+                                                          float* __restrict__ vt_lo, int L, int C) {
+  __shared__ float tile[32][33];
+  const int l0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const size_t b = blockIdx.z;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;       // 32 x 8
+  const float* src = qkv + b * (size_t)L * 3 * C;
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    const int l = l0 + ty + j, c = c0 + tx;
+    const float kv = src[(size_t)l * 3 * C + C + c];
+    uint32_t h;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(kv));
+    h &= 0xffffe000u;
+    const size_t o = (b * L + l) * C + c;
+    k_hi[o] = __uint_as_float(h);
+    k_lo[o] = kv - __uint_as_float(h);
+    tile[ty + j][tx] = src[(size_t)l * 3 * C + 2 * C + c];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < 32; j += 8) {
+    const int c = c0 + ty + j, l = l0 + tx;
+    const float v = tile[tx][ty + j];
+    uint32_t h;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(h) : "f"(v));
+    h &= 0xffffe000u;
+    const size_t o = (b * C + c) * L + l;
+    vt_hi[o] = __uint_as_float(h);
+    vt_lo[o] = v - __uint_as_float(h);
+  }
+}
+
 // w -> (tf32(w), w - tf32(w)), elementwise (weights are split once per load_state_dict, not per launch)
 __global__ void split_tf32_kernel(const float* __restrict__ w, float* __restrict__ hi, float* __restrict__ lo, long long n) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -323,6 +381,7 @@ extern "C" int b200_conv2d_tc32(const float* x1, int C1, const float* x2, int C2
   p.num_m = p.TB > 1 ? (B + p.TB - 1) / p.TB : B * p.tiles_w * p.tiles_h;
   p.num_n = Cout / T32_BN;
   p.terms = terms;
+  p.w_batched = 0;
   // terms = 3: every K block is drained (12 MMAs per partial sum): the full networks then sit as close to the fp64 run of
   // the reference as the reference's own fp32 run does (profiles/r02h_strict_accuracy.txt: DDPM 64x64 2.0e-6 with 1,
   // 3.4e-6 with 2, 6.6e-6 with 4 K blocks per group; reference fp32 2.1e-6) for 7 % of the speed.  terms = 1: the tf32
@@ -354,5 +413,58 @@ extern "C" int b200_conv2d_tc32(const float* x1, int C1, const float* x2, int C2
   const int tiles = p.num_m * p.num_n;
   const int grid = tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS;
   conv_tc32_kernel<<<grid, T32_THREADS, T32_SMEM, st>>>(a1, a2, wh, wl, p);
+  B200_RETURN_LAST();
+}
+
+// Batched GEMM on the same kernel: out[b][m][n] = scale * sum_k a[b][m][k] * bm[b][n][k]  (fp32; bm pre-split into hi / lo
+// by b200_split_tf32; a's rows `lda` floats apart).  The two products of the strict-mode attention (q k^T and p v with
+// v transposed, models/layerspp.py:82-86).  M % 128 == N % 128 == K % 32 == 0.
+extern "C" int b200_gemm_tc32_batched(const float* a, long long lda, const float* b_hi, const float* b_lo, float* out, int B,
+                                      int M, int N, int K, float scale, int terms, cudaStream_t st) {
+  if (!a || !b_hi || !out || (terms != 1 && terms != 3) || (terms == 3 && !b_lo) || B < 0 || lda < K) return B200_ERR_ARG;
+  if (M <= 0 || M % T32_BM || N <= 0 || N % T32_BN || K <= 0 || K % T32_BK || (lda * 4) % 16) return B200_ERR_UNSUPPORTED;
+  if (B == 0) return B200_OK;
+  static const int flush_env = [] { const char* e = getenv("B200_TC32_FLUSH"); return e ? atoi(e) : 0; }();
+  Conv32Params p;
+  p.B = B; p.H = M / T32_BM; p.W = T32_BM; p.C1 = K; p.C2 = 0; p.Cout = N; p.taps_w = 1; p.pad = 0;
+  p.TW = T32_BM; p.TH = 1; p.TB = 1; p.tiles_w = 1; p.tiles_h = p.H;
+  p.num_m = B * p.H; p.num_n = N / T32_BN;
+  p.terms = terms; p.flush = flush_env > 0 ? flush_env : (terms == 3 ? 1 : 8); p.w_batched = 1;
+  p.bias = nullptr; p.temb = nullptr; p.temb_stride = 0; p.res = nullptr; p.out_scale = scale; p.out = out;
+  CUtensorMap am, wh, wl;
+  {
+    const uint64_t dims[4] = {(uint64_t)K, (uint64_t)T32_BM, (uint64_t)p.H, (uint64_t)B};
+    const uint64_t strides[3] = {(uint64_t)lda * 4, (uint64_t)T32_BM * lda * 4, (uint64_t)M * lda * 4};
+    const uint32_t box[4] = {(uint32_t)T32_BK, (uint32_t)T32_BM, 1u, 1u};
+    if (int rc = tc_tensor_map(&am, a, 4, dims, strides, box, 0, nullptr, 1)) return rc;
+  }
+  auto bmap = [&](CUtensorMap* m, const float* ptr) {
+    const uint64_t dims[3] = {(uint64_t)K, (uint64_t)N, (uint64_t)B};
+    const uint64_t strides[2] = {(uint64_t)K * 4, (uint64_t)N * K * 4};
+    const uint32_t box[3] = {(uint32_t)T32_BK, (uint32_t)T32_BN, 1u};
+    return tc_tensor_map(m, ptr, 3, dims, strides, box, 1, nullptr, 1);
+  };
+  if (int rc = bmap(&wh, b_hi)) return rc;
+  if (terms == 3) { if (int rc = bmap(&wl, b_lo)) return rc; } else wl = wh;
+  static int attr_state[B200_MAX_DEVICES];
+  if (int r2 = b200_set_smem_once(attr_state, conv_tc32_kernel, T32_SMEM)) return r2;
+  const int tiles = p.num_m * p.num_n;
+  conv_tc32_kernel<<<tiles < B200_NUM_SMS ? tiles : B200_NUM_SMS, T32_THREADS, T32_SMEM, st>>>(am, am, wh, wl, p);
+  B200_RETURN_LAST();
+}
+
+extern "C" int b200_softmax_rows_f32(float* x, long long rows, int n, cudaStream_t st) {
+  if (!x || rows < 0 || n <= 0) return B200_ERR_ARG;
+  if (rows == 0) return B200_OK;
+  softmax_rows_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(x, rows, n);
+  B200_RETURN_LAST();
+}
+
+extern "C" int b200_attn32_prep(const float* qkv, float* k_hi, float* k_lo, float* vt_hi, float* vt_lo, int B, int L, int C,
+                                cudaStream_t st) {
+  if (!qkv || !k_hi || !k_lo || !vt_hi || !vt_lo || B < 0 || B > 65535) return B200_ERR_ARG;
+  if (L <= 0 || L % 32 || C <= 0 || C % 32) return B200_ERR_UNSUPPORTED;
+  if (B == 0) return B200_OK;
+  attn32_prep_kernel<<<dim3(L / 32, C / 32, B), 256, 0, st>>>(qkv, k_hi, k_lo, vt_hi, vt_lo, L, C);
   B200_RETURN_LAST();
 }

@@ -718,6 +718,9 @@ class ScoreEngine:
         if self.use_tc and tc.attention_supported(L, C):
             tc.emit_attention(b, qkv, out, L, C)
             return
+        if self.tc32_terms and self.dt == DT_F32 and tc.attention32_supported(L, C):
+            tc.emit_attention32(b, qkv, out, L, C, self.tc32_terms)
+            return
         b.emit("b200_attention_simt", qkv, qkv.at(C * es), qkv.at(2 * C * es), out, self.dt, b.B, L, C, 3 * C, 3 * C,
                3 * C, C, float(int(C) ** (-0.5)), flops=4 * b.B * L * L * C)
 

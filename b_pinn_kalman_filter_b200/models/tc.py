@@ -31,6 +31,10 @@ _lib.register_signature("b200_conv2d_tc32_supported", [c_int] * 7)
 _lib.register_signature("b200_conv2d_tc32", [c_vp, c_int, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_float, c_vp]
                         + [c_int] * 6 + [c_vp])
 
+_lib.register_signature("b200_gemm_tc32_batched", [c_vp, c_ll, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_float, c_int, c_vp])
+_lib.register_signature("b200_softmax_rows_f32", [c_vp, c_ll, c_int, c_vp])
+_lib.register_signature("b200_attn32_prep", [c_vp, c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_int, c_vp])
+
 ENABLED = True
 FUSE_SHORTCUT = True  # Conv_2 (1x1 shortcut) folded into Conv_1's K loop (b200_conv2d_tc_sc)
 FUSE_GN = True        # GroupNorm + SiLU inside the consumer conv's operand pipeline (b200_conv2d_tc_gn)
@@ -64,6 +68,25 @@ def emit_conv32(b, x, x2, w_hi, w_lo, bias, temb_ptr, res, out_scale, out, ksize
     b.emit("b200_conv2d_tc32", x, x.C, p2, c2, w_hi.data_ptr(), w_lo.data_ptr(), bias.data_ptr(), temb_ptr, b.temb_stride,
            res, out_scale, out, b.B, x.H, x.W, out.C, ksize, terms, flops=flops,
            tag="%dx%d %dx%d %d->%d tf32x%d" % (ksize, ksize, x.H, x.W, x.C + c2, out.C, terms))
+
+
+def attention32_supported(L, C):
+    """Strict-mode attention as two batched tf32-split GEMMs around a row softmax."""
+    return ENABLED and L % 128 == 0 and C % 128 == 0
+
+
+def emit_attention32(b, qkv, out, L, C, terms):
+    """softmax(q k^T / sqrt(C)) v in fp32 on the tensor cores (models/layerspp.py:82-86): operand preparation (k split, v
+    transposed and split), q k^T -> scores [B, L, L], row softmax, p v."""
+    kh, kl = b.new(qkv.H, qkv.W, C), b.new(qkv.H, qkv.W, C)
+    vh, vl = b.new(qkv.H, qkv.W, C), b.new(qkv.H, qkv.W, C)
+    sc = b.new(qkv.H, qkv.W, L)
+    b.emit("b200_attn32_prep", qkv, kh, kl, vh, vl, b.B, L, C)
+    b.emit("b200_gemm_tc32_batched", qkv, 3 * C, kh, kl, sc, b.B, L, L, C, float(int(C) ** (-0.5)), terms,
+           flops=2 * b.B * L * L * C, tag="q k^T %dx%dx%d tf32x%d" % (L, L, C, terms))
+    b.emit("b200_softmax_rows_f32", sc, b.B * L, L)
+    b.emit("b200_gemm_tc32_batched", sc, L, vh, vl, out, b.B, L, C, L, 1.0, terms,
+           flops=2 * b.B * L * L * C, tag="p v %dx%dx%d tf32x%d" % (L, C, L, terms))
 
 
 def conv_gn_supported(b, x1, x2, out, ksize, stride, pad):

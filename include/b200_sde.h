@@ -151,6 +151,14 @@ int b200_conv2d_tc32_supported(int C1, int C2, int B, int H, int W, int Cout, in
 int b200_conv2d_tc32(const float* x1, int C1, const float* x2, int C2, const float* w_hi, const float* w_lo,
                      const float* bias, const float* temb, int temb_stride, const float* res, float out_scale,
                      float* out, int B, int H, int W, int Cout, int ksize, int terms, cudaStream_t stream);
+/* the same kernel as a batched GEMM, out[b][m][n] = scale * sum_k a[b][m][k] bm[b][n][k] (a's rows lda floats apart, bm
+ * pre-split), and a row softmax: the strict-mode attention q k^T -> softmax -> p v (models/layerspp.py:82-86) */
+int b200_gemm_tc32_batched(const float* a, long long lda, const float* b_hi, const float* b_lo, float* out, int B, int M,
+                           int N, int K, float scale, int terms, cudaStream_t stream);
+int b200_softmax_rows_f32(float* x, long long rows, int n, cudaStream_t stream);
+/* qkv [B][L][3C] -> k as (hi, lo) [B][L][C] and v transposed as (hi, lo) [B][C][L]: the B operands of the two products */
+int b200_attn32_prep(const float* qkv, float* k_hi, float* k_lo, float* vt_hi, float* vt_lo, int B, int L, int C,
+                     cudaStream_t stream);
 /* implicit-GEMM convolution on CUDA cores (strict fp32 path + odd shapes); epilogue
  * out = ((conv + bias[n] + temb[b,n]) + res) * out_scale.  replaces nn.Conv2d / NIN (models/layers.py:96-118,537-546) */
 int b200_conv2d_simt(const void* x1, int C1, const void* x2, int C2, const void* w, const float* bias,

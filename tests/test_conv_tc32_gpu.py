@@ -109,3 +109,43 @@ def test_strict_network_on_tensor_cores(cuda, name):
                 m.engine.tc32_convs, m.engine.simt_convs)
     assert errs["fp32"] < 3 * errs["fp32_simt"] + 1e-6, errs
     assert errs["tf32"] > errs["fp32"], errs
+
+
+@pytest.mark.parametrize("B,L,C", [(3, 256, 256), (2, 128, 384)])
+def test_strict_attention_on_tensor_cores(cuda, B, L, C):
+    """q k^T -> softmax -> p v as two batched tf32-split GEMMs (b200_attn32_prep + b200_gemm_tc32_batched +
+    b200_softmax_rows_f32) against the exact attention of the same fp32 operands (models/layerspp.py:82-86)."""
+    _lib = _sig()
+    lib = _lib.lib()
+    g = torch.Generator().manual_seed(B + L + C)
+    qkv = (torch.randn(B, L, 3 * C, generator=g) * 1.3).to(cuda)
+    q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
+
+    def ref(dt):
+        w = torch.einsum("blc,bmc->blm", q.to(dt), k.to(dt)) * (int(C) ** (-0.5))
+        return torch.einsum("blm,bmc->blc", torch.softmax(w, -1), v.to(dt))
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        exact = ref(torch.float64)
+        e_torch = (ref(torch.float32).double() - exact).abs().max().item()
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+    kh, kl, vh, vl = (torch.empty(B, L, C, device=cuda) for _ in range(4))
+    sc = torch.empty(B, L, L, device=cuda)
+    out = torch.full((B, L, C), float("nan"), device=cuda)
+    st = _lib.stream()
+    P = _lib.ptr
+    _lib.check(lib.b200_attn32_prep(P(qkv), P(kh), P(kl), P(vh), P(vl), B, L, C, st), "prep")
+    assert torch.equal(kh + kl, k) and torch.equal((vh + vl).view(B, C, L), v.transpose(1, 2))
+    errs = {}
+    for terms in (3, 1):
+        _lib.check(lib.b200_gemm_tc32_batched(P(qkv), 3 * C, P(kh), P(kl), P(sc), B, L, L, C, int(C) ** (-0.5), terms, st), "qk")
+        _lib.check(lib.b200_softmax_rows_f32(P(sc), B * L, L, st), "softmax")
+        _lib.check(lib.b200_gemm_tc32_batched(P(sc), L, P(vh), P(vl), P(out), B, L, C, L, 1.0, terms, st), "pv")
+        torch.cuda.synchronize()
+        assert torch.isfinite(out).all()
+        errs[terms] = (out.double() - exact).abs().max().item()
+    top = exact.abs().max().item()
+    assert errs[3] <= max(2.0 * e_torch, 1e-6 * top), (errs, e_torch, top)
+    assert errs[3] < errs[1] < 1e-2 * top, (errs, top)
