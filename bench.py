@@ -376,8 +376,8 @@ def other_config_measurements(dev, timeit):
         res["C3_training_step"] = {"batch": Bt, "ms_per_step": ms, "images_per_s": Bt / ms * 1e3, "loss_first": l0,
                                    "loss_last": float(tr.loss[0]), "launches": len(tr.plan.ops),
                                    "parameters": tr.n, "finite": bool(torch.isfinite(tr.flat_p).all()),
-                                   "note": "weight gradients on b200_conv2d_tc over K = pixels; per-step weight "
-                                           "re-packing and gradient re-layout are torch copies (host-bound)"}
+                                   "note": "weight gradients on b200_conv2d_tc over K = pixels; gradient "
+                                           "collection and weight re-packing are one b200_copy_batch launch each"}
         del mt, state, tr
         torch.cuda.empty_cache()
     except Exception as e:  # noqa: BLE001
@@ -628,7 +628,7 @@ def run_b200(a):
         traffic, traffic_src = tj.get("dram_bytes_per_launch"), "profiles/conv_tc_traffic.json (%s, %d launches)" % (
             tj.get("source", "ncu --set full"), tj.get("launches", 0))
     roof = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tc_sustained"], "unit": "TFLOP/s",
-            "frac": achieved / pk["tc_sustained"], "traffic": traffic, "traffic_unit": "bytes per launch (DRAM read + write)",
+            "frac": achieved / pk["tc_sustained"], "frac_of_burst_peak": achieved / pk["tc_burst"], "traffic": traffic, "traffic_unit": "bytes per launch (DRAM read + write)",
             "traffic_source": traffic_src, "peak_source": pk["source"] + " (sustained bf16)",
             "launches_per_forward": n_l, "avg_launch_ms": d_ms / max(n_l, 1),
             "flops_per_forward": d_fl, "share_of_forward": d_ms / fwd_ms if fwd_ms else None}
