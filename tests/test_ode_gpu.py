@@ -150,13 +150,13 @@ def test_dps_sampler_device_solver_matches_scipy_driver(cuda):
     sampler = cs.get_sampler(config, obsv, shape, eps=0.99)
     xd = sampler(m, z=z.clone())
     xs = sampler(m, z=z.clone(), solver="scipy")
-        assert xd.shape == shape and torch.isfinite(xd).all()
-        # The two drivers take the same decisions (same number of right-hand sides: profiles show 476 / 476 here), but
-        # their stage sums differ in the last fp64 bit (numpy dot vs the rk_stage kernel's order), which now and then
-        # rounds one fp32 network input differently; the bf16 network and the stiff guided ODE amplify that to 1e-4 ..
-        # 4e-3 of the solution (0.0 for most observation draws).  Both are solutions to rtol = atol = 1e-3, so the bar is
-        # the solver's own tolerance; step-for-step identity with scipy is asserted on the smooth right-hand sides above.
-        assert cases.rel_l2(xd.cpu(), xs.cpu()) < 2e-2
+    assert xd.shape == shape and torch.isfinite(xd).all()
+    # The two drivers take the same decisions (same number of right-hand sides: 476 / 476 here), but their stage sums
+    # differ in the last fp64 bit (numpy dot vs the rk_stage kernel's order), which now and then rounds one fp32 network
+    # input differently; the bf16 network and the stiff guided ODE amplify that to 1e-4 .. 4e-3 of the solution (0.0 for
+    # most observation draws).  Both are solutions to rtol = atol = 1e-3, so the bar is the solver's own tolerance;
+    # step-for-step identity with scipy is asserted on the smooth right-hand sides above.
+    assert cases.rel_l2(xd.cpu(), xs.cpu()) < 2e-2
 
 
 def test_fixed_solver_device_matches_host_loop(cuda):
