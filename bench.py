@@ -320,7 +320,7 @@ def other_config_measurements(dev, timeit):
         S, C = cfg.data.image_size, cfg.data.num_channels
         y = m(torch.randn(B, C, S, S, device=dev), torch.rand(B, device=dev) * 10 + 0.1)
         plan = m.engine.plan(B)
-        ms = timeit(lambda: plan.run(_lib.stream()), iters=5)
+        ms = timeit(lambda: m.engine._run_ops(plan, "all", plan.ops), iters=5)     # as model(x, t) runs it: graph replay
         res[tag] = {"batch": B, "ms_per_forward": ms, "tflops": plan.flops() / ms / 1e9, "launches": len(plan.ops),
                     "samples_per_s_per_gpu": B / (ms * 1e-3 * fwd_per_sample), "finite": bool(torch.isfinite(y).all())}
         # the same config END TO END through the public API (get_pc_sampler: host prior -> H2D, PC steps, samples -> D2H)
