@@ -477,6 +477,34 @@ extern "C" int b200_adam_ema(float* p, float* m, float* v, float* ema, const flo
   B200_RETURN_LAST();
 }
 
+// ---- out[i] = sum_s in[s][i]  (the S partial products of b200_gemm_tc_splitk; 8 elements per thread, fixed order) -------
+namespace b200 {
+template <typename T>
+__global__ void __launch_bounds__(256) sum_partials_kernel(const T* __restrict__ in, float* __restrict__ out, int S, long long n) {
+  for (long long i = (blockIdx.x * (long long)blockDim.x + threadIdx.x) * 8; i < n; i += (long long)gridDim.x * blockDim.x * 8) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+    for (int s = 0; s < S; ++s) {
+      float v[8];
+      Vec8<T>::load(in + (size_t)s * n + i, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+    *reinterpret_cast<float4*>(out + i) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    *reinterpret_cast<float4*>(out + i + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  }
+}
+}  // namespace b200
+
+extern "C" int b200_sum_partials(const void* in, float* out, int dtype, int S, long long n, cudaStream_t st) {
+  if (!in || !out || S <= 0 || n <= 0 || n % 8) return B200_ERR_ARG;
+  if (dtype == B200_DT_F32) sum_partials_kernel<float><<<tr_grid(n / 8), 256, 0, st>>>((const float*)in, out, S, n);
+  else if (dtype == B200_DT_BF16) sum_partials_kernel<bf16><<<tr_grid(n / 8), 256, 0, st>>>((const bf16*)in, out, S, n);
+  else return B200_ERR_ARG;
+  B200_RETURN_LAST();
+}
+
 // ---- batched strided copy --------------------------------------------------------------------------------------------
 // After every optimizer step the plans' derived weight copies have to follow the flat fp32 parameters: forward weights
 // re-packed to [Cout][kh][kw][Cin] bf16 (NIN transposed, q/k/v and the 1x1 shortcuts stacked), backward-data weights

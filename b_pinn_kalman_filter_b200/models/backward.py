@@ -37,6 +37,7 @@ _lib.register_signature("b200_attention_bwd", [c_vp, c_vp, c_vp, c_vp, c_int, c_
 # training (csrc/train.cu)
 _lib.register_signature("b200_transpose2d", [c_vp, c_vp, c_int, c_ll, c_int, c_vp])
 _lib.register_signature("b200_im2col_t", [c_vp, c_int, c_vp, c_int, c_vp, c_int] + [c_int] * 8 + [c_vp])
+_lib.register_signature("b200_sum_partials", [c_vp, c_vp, c_int, c_int, c_ll, c_vp])
 _lib.register_signature("b200_colsum", [c_vp, c_vp, c_int, c_int, c_ll, c_int, c_ll, c_float, c_int, c_vp])
 _lib.register_signature("b200_gn_param_grad", [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp,
                                                c_vp, c_float, c_int, c_vp, c_vp])
@@ -259,13 +260,29 @@ def _conv_param_grads(b, t, gy, scale):
         xT = xT_t.data_ptr()
     else:
         xT = Act(None, 1, 1, kout, P)
-    gw = torch.zeros(cout_s, kpad, device=b.e.device, dtype=_TORCH_DT[b.dt])
+    # split K = pixels over S "images" of a batched 1x1 convolution (b200_gemm_tc_splitk) so that tiles x S CTAs, not 9-18,
+    # share the loop; the bf16 partial products are summed in fp32 by b200_sum_partials
+    split = 0
+    if (b.e.use_tc and tc.ENABLED and os.environ.get("B200_WGRAD_SPLITK", "1") != "0" and cout_s % 128 == 0
+            and kpad % 128 == 0 and P % 64 == 0):
+        tiles = (cout_s // 128) * (kpad // (256 if kpad % 256 == 0 else 128))
+        split = 1
+        while split < 64 and tiles * split < 120 and P % (2 * split * 64) == 0 and P // (2 * split) >= 512:
+            split *= 2
+        if split == 1:
+            split = 0
+    gw = torch.zeros(cout_s, kpad, device=b.e.device, dtype=torch.float32 if split else _TORCH_DT[b.dt])
     b.plan.keep.append(gw)
     b.emit("b200_transpose2d", gy, gyT, b.dt, P, cout_s)
     p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
     b.emit("b200_im2col_t", x, x.C, p2, c2, xT, b.dt, b.B, x.H, x.W, Ho, Wo, k, stride, pad[0])
     flops = 2 * P * cout_s * kout
-    if b.e.use_tc and tc.ENABLED and _lib.lib().b200_conv2d_tc_supported(P, 0, 1, 1, cout_s, kpad, 1, 1, 0):
+    if split:
+        part = Act(None, split, 1, cout_s, kpad)
+        b.emit("b200_gemm_tc_splitk", gyT, P, xT, P, part, cout_s, kpad, P, split, flops=flops,
+               tag="wgrad %dx%d %dx%d %d->%d split %d" % (k, k, Ho, Wo, cin_s, cout_s, split))
+        b.emit("b200_sum_partials", part, gw.data_ptr(), b.dt, split, cout_s * kpad)
+    elif b.e.use_tc and tc.ENABLED and _lib.lib().b200_conv2d_tc_supported(P, 0, 1, 1, cout_s, kpad, 1, 1, 0):
         b.emit("b200_conv2d_tc", gyT, P, None, 0, xT, None, None, 0, None, 1.0, gw.data_ptr(), 0, None, None, 1, 1, cout_s,
                kpad, 1, flops=flops, tag="wgrad %dx%d %dx%d %d->%d" % (k, k, Ho, Wo, cin_s, cout_s))
     else:

@@ -311,6 +311,12 @@ int b200_dropout(void* y, const void* x, int dtype, long long n, float p, uint64
 int b200_grad_sumsq(float* sumsq, const float* g, long long n, cudaStream_t stream);
 int b200_adam_ema(float* p, float* m, float* v, float* ema, const float* g, const float* hyper, const float* sumsq,
                   float grad_scale, long long n, cudaStream_t stream);
+/* split-K batched GEMM on the tensor-core 1x1 path: out[s][m][n] = sum over the s-th of S K chunks of a[m][k] bm[n][k]
+ * (bf16, row strides lda / ldb elements); the weight-gradient GEMMs over K = pixels (autograd's conv weight backward,
+ * losses.py:196).  M % 128 == N % 128 == 0, (K / S) % 64 == 0.  b200_sum_partials: out[i] = sum_s in[s][i] (fp32), i < n, n % 8 == 0. */
+int b200_sum_partials(const void* in, float* out, int dtype, int S, long long n, cudaStream_t stream);
+int b200_gemm_tc_splitk(const void* a, long long lda, const void* bm, long long ldb, void* out, int M, int N, long long K,
+                        int S, cudaStream_t stream);
 /* One launch for a table of <= 4-D strided copies with scale and fp32 <-> bf16 conversion (dst[i] = scale * (src[j(i)] +
  * src2[j(i)])): what keeps the plans' packed / flipped weight copies and the flat gradient buffer in step with the flat
  * parameters after optimizer.step() (the reference re-reads its nn.Parameters in place; no counterpart).  Descriptor

@@ -52,3 +52,15 @@ print("--- device time per entry point (events around every launch)")
 for k, v in sorted(tab.items(), key=lambda kv: -kv[1][1])[:14]:
     print("%-34s n=%4d %8.2f ms" % (k, v[0], v[1]))
 print("sum %.2f ms" % sum(v[1] for v in tab.values()))
+# the convolution launches by role (forward / backward-data / weight gradient) and, for the weight gradients, by shape
+role = {}
+for (name, e0, e1), tag in zip(evs, p.tags):
+    if not name.startswith("b200_conv2d"):
+        continue
+    r = "wgrad" if tag.startswith("wgrad") else ("dgrad" if tag.startswith("dgrad") else "forward / other")
+    a = role.setdefault(r, [0, 0.0]); a[0] += 1; a[1] += e0.elapsed_time(e1)
+    if r == "wgrad":
+        a = role.setdefault("  " + tag, [0, 0.0]); a[0] += 1; a[1] += e0.elapsed_time(e1)
+print("--- convolution launches by role")
+for k, v in sorted(role.items(), key=lambda kv: (kv[0].startswith("  "), -kv[1][1]))[:24]:
+    print("%-44s n=%4d %8.2f ms" % (k, v[0], v[1]))
