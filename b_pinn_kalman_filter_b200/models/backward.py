@@ -273,11 +273,23 @@ def _conv_param_grads(b, t, gy, scale):
             split = 0
     gw = torch.zeros(cout_s, kpad, device=b.e.device, dtype=torch.float32 if split else _TORCH_DT[b.dt])
     b.plan.keep.append(gw)
-    b.emit("b200_transpose2d", gy, gyT, b.dt, P, cout_s)
     p2, c2 = (x2, x2.C) if x2 is not None else (None, 0)
-    b.emit("b200_im2col_t", x, x.C, p2, c2, xT, b.dt, b.B, x.H, x.W, Ho, Wo, k, stride, pad[0])
     flops = 2 * P * cout_s * kout
-    if split:
+    direct = (split and stride == 1 and tuple(pad) == (k // 2, k // 2) and (Ho, Wo) == (x.H, x.W) and kpad == kout
+              and os.environ.get("B200_WGRAD_DIRECT", "1") != "0"
+              and _lib.lib().b200_wgrad_tc_supported(cout_s, x.C, c2, b.B, x.H, x.W, k, split))
+    if direct:
+        # straight from the channels-last tensors: MN-major operands, tap shifts as TMA box coordinates (b200_wgrad_tc)
+        part = Act(None, split, 1, cout_s, kpad)
+        b.emit("b200_wgrad_tc", gy, x, x.C, p2, c2, part, cout_s, b.B, x.H, x.W, k, split, flops=flops,
+               tag="wgrad %dx%d %dx%d %d->%d direct split %d" % (k, k, Ho, Wo, cin_s, cout_s, split))
+        b.emit("b200_sum_partials", part, gw.data_ptr(), b.dt, split, cout_s * kpad)
+    else:
+        b.emit("b200_transpose2d", gy, gyT, b.dt, P, cout_s)
+        b.emit("b200_im2col_t", x, x.C, p2, c2, xT, b.dt, b.B, x.H, x.W, Ho, Wo, k, stride, pad[0])
+    if direct:
+        pass
+    elif split:
         part = Act(None, split, 1, cout_s, kpad)
         b.emit("b200_gemm_tc_splitk", gyT, P, xT, P, part, cout_s, kpad, P, split, flops=flops,
                tag="wgrad %dx%d %dx%d %d->%d split %d" % (k, k, Ho, Wo, cin_s, cout_s, split))

@@ -37,6 +37,9 @@ _lib.register_signature("b200_attn32_prep", [c_vp, c_vp, c_vp, c_vp, c_vp, c_int
 
 _lib.register_signature("b200_gemm_tc_splitk", [c_vp, c_ll, c_vp, c_ll, c_vp, c_int, c_int, c_ll, c_int, c_vp])
 
+_lib.register_signature("b200_wgrad_tc_supported", [c_int] * 8)
+_lib.register_signature("b200_wgrad_tc", [c_vp, c_vp, c_int, c_vp, c_int, c_vp] + [c_int] * 6 + [c_vp])
+
 ENABLED = True
 FUSE_SHORTCUT = True  # Conv_2 (1x1 shortcut) folded into Conv_1's K loop (b200_conv2d_tc_sc)
 FUSE_GN = True        # GroupNorm + SiLU inside the consumer conv's operand pipeline (b200_conv2d_tc_gn)

@@ -314,6 +314,13 @@ int b200_adam_ema(float* p, float* m, float* v, float* ema, const float* g, cons
 /* split-K batched GEMM on the tensor-core 1x1 path: out[s][m][n] = sum over the s-th of S K chunks of a[m][k] bm[n][k]
  * (bf16, row strides lda / ldb elements); the weight-gradient GEMMs over K = pixels (autograd's conv weight backward,
  * losses.py:196).  M % 128 == N % 128 == 0, (K / S) % 64 == 0.  b200_sum_partials: out[i] = sum_s in[s][i] (fp32), i < n, n % 8 == 0. */
+/* weight gradient of a stride-1 "same" convolution, split over S chunks of pixels, straight from the channels-last
+ * tensors (no transpose, no im2col): out[s][co][(tap, ci)] = sum_{p in chunk s} gy[p][co] x[p + tap][ci]; gy = dY [P][M],
+ * x1 / x2 = the conv's source(s) [P][C] (P = B H W); MN-major MMA operands, the tap shift and the zero padding are TMA box
+ * coordinates.  M % 128 == 0, C % 64 == 0, (P / S) % 64 == 0, rows of <= 64 pixels tile 64-pixel K blocks. */
+int b200_wgrad_tc_supported(int M, int C1, int C2, int B, int H, int W, int ksize, int S);
+int b200_wgrad_tc(const void* gy, const void* x1, int C1, const void* x2, int C2, void* out, int M, int B, int H, int W,
+                  int ksize, int S, cudaStream_t stream);
 int b200_sum_partials(const void* in, float* out, int dtype, int S, long long n, cudaStream_t stream);
 int b200_gemm_tc_splitk(const void* a, long long lda, const void* bm, long long ldb, void* out, int M, int N, long long K,
                         int S, cudaStream_t stream);

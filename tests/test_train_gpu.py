@@ -219,3 +219,50 @@ def test_descriptor_table_refresh_equals_torch_refresh(cuda, name, precision):
     assert l0 == l1, (l0, l1)
     assert all(torch.equal(a, b) for a, b in zip(p0, p1))
     assert all(torch.equal(a, b) for a, b in zip(e0, e1))
+
+
+@pytest.mark.parametrize("shape", [  # B, H, C1, C2, Cout, k, S
+    (16, 32, 128, 0, 128, 3, 16),      # K block = 2 rows of 32
+    (8, 16, 256, 256, 256, 3, 4),      # two sources, K block = 4 rows of 16, 256-wide N tiles
+    (8, 16, 256, 128, 256, 3, 4),      # two sources of different width -> 128-wide N tiles
+    (32, 8, 256, 0, 256, 3, 8),        # K block = one 8 x 8 image
+    (64, 4, 256, 0, 256, 3, 2),        # K block = four 4 x 4 images
+    (8, 16, 512, 0, 256, 1, 4),        # 1x1
+    (2, 64, 128, 0, 128, 3, 8),        # K block = one row of 64
+])
+def test_direct_weight_gradient_without_im2col(cuda, shape):
+    """b200_wgrad_tc (MN-major operands straight from the channels-last tensors, TMA tap shifts, S pixel chunks) + b200_sum_partials against
+    torch.nn.grad.conv2d_weight on the same bf16-rounded operands, and against the split-K GEMM over the materialised
+    transposed im2col (b200_im2col_t + b200_gemm_tc_splitk), which must give the same bits."""
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import backward, tc  # noqa: F401
+    B, H, C1, C2, Cout, k, S = shape
+    lib = _lib.lib()
+    gen = torch.Generator().manual_seed(sum(shape))
+    x1 = torch.randn(B, H, H, C1, generator=gen).to(cuda, torch.bfloat16)
+    x2 = torch.randn(B, H, H, C2, generator=gen).to(cuda, torch.bfloat16) if C2 else None
+    gy = torch.randn(B, H, H, Cout, generator=gen).to(cuda, torch.bfloat16)
+    P, Ct = B * H * H, C1 + C2
+    N = k * k * Ct
+    bf = dict(device=cuda, dtype=torch.bfloat16)
+    gyT = torch.empty(Cout, P, **bf)
+    st = _lib.stream()
+    P_ = _lib.ptr
+    _lib.check(lib.b200_transpose2d(P_(gy), P_(gyT), 1, P, Cout, st), "transpose")
+    assert lib.b200_wgrad_tc_supported(Cout, C1, C2, B, H, H, k, S) == 1
+    part = torch.full((S, Cout, N), float("nan"), **bf)
+    _lib.check(lib.b200_wgrad_tc(P_(gy), P_(x1), C1, P_(x2), C2, P_(part), Cout, B, H, H, k, S, st), "b200_wgrad_tc")
+    gw = torch.empty(Cout, N, device=cuda)
+    _lib.check(lib.b200_sum_partials(P_(part), P_(gw), 1, S, Cout * N, st), "b200_sum_partials")
+    # the same split through the materialised transposed im2col
+    xT = torch.empty(N, P, **bf)
+    _lib.check(lib.b200_im2col_t(P_(x1), C1, P_(x2), C2, P_(xT), 1, B, H, H, H, H, k, 1, k // 2, st), "im2col_t")
+    part2 = torch.full((S, Cout, N), float("nan"), **bf)
+    _lib.check(lib.b200_gemm_tc_splitk(P_(gyT), P, P_(xT), P, P_(part2), Cout, N, P, S, st), "b200_gemm_tc_splitk")
+    torch.cuda.synchronize()
+    assert torch.isfinite(part.float()).all()
+    assert torch.equal(part, part2), (part.float() - part2.float()).abs().max().item()
+    xx = (torch.cat([x1, x2], -1) if C2 else x1).float().permute(0, 3, 1, 2)
+    ref = torch.nn.grad.conv2d_weight(xx, (Cout, Ct, k, k), gy.float().permute(0, 3, 1, 2), stride=1, padding=k // 2)
+    got = gw.view(Cout, k, k, Ct).permute(0, 3, 1, 2)
+    assert cases.rel_l2(got.cpu(), ref.cpu()) < 4e-3, cases.rel_l2(got.cpu(), ref.cpu())
