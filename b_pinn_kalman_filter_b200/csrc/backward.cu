@@ -23,6 +23,7 @@ struct GnBwdArgs {
   const void* dy;               // [B, HW, C1 + C2]
   void* dx1; void* dx2;         // gradients of the sources (dx2 null when C2 == 0)
   int acc1, acc2;               // 1: add to what dx already holds
+  float* chan_sums;             // optional [B, nsplit, C, 2]: (sum dz xhat, sum dz) per channel = the pieces of d gamma, d beta
 };
 
 __device__ __forceinline__ void gn_bwd_stats(const GnBwdArgs& a, int b, float* sh) {
@@ -42,14 +43,18 @@ __device__ __forceinline__ void gn_bwd_stats(const GnBwdArgs& a, int b, float* s
   }
 }
 
-// t = d(loss)/d(xhat) = dy * act'(z) * gamma, with z = gamma * xhat + beta
-__device__ __forceinline__ float gn_bwd_t(float dy, float xhat, float ga, float be, int act) {
+// dz = d(loss)/d(z) = dy * act'(z), with z = gamma * xhat + beta
+__device__ __forceinline__ float gn_bwd_dz(float dy, float xhat, float ga, float be, int act) {
   if (act) {
     const float z = fmaf(ga, xhat, be);
     const float sg = 1.0f / (1.0f + __expf(-z));
     dy *= sg * (1.0f + z * (1.0f - sg));
   }
-  return dy * ga;
+  return dy;
+}
+// t = d(loss)/d(xhat) = dz * gamma
+__device__ __forceinline__ float gn_bwd_t(float dy, float xhat, float ga, float be, int act) {
+  return gn_bwd_dz(dy, xhat, ga, be, act) * ga;
 }
 
 template <typename T>
@@ -82,8 +87,8 @@ __global__ void __launch_bounds__(256) gn_bwd_partial_kernel(GnBwdArgs a) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float xh = (v[j] - mu[j]) * rs[j];
-      const float t = gn_bwd_t(d[j], xh, ga[j], be[j], a.act);
-      s1[j] += t; s2[j] = fmaf(t, xh, s2[j]);
+      const float dz = gn_bwd_dz(d[j], xh, ga[j], be[j], a.act);     // per-channel sums of dz: gamma comes in at the fold
+      s1[j] += dz; s2[j] = fmaf(dz, xh, s2[j]);
     }
   }
 #pragma unroll
@@ -95,9 +100,19 @@ __global__ void __launch_bounds__(256) gn_bwd_partial_kernel(GnBwdArgs a) {
     acc[i] = t;
   }
   __syncthreads();
+  if (a.chan_sums) {
+    // the same sums are the block's share of d beta (sum dz) and d gamma (sum dz xhat): training plans take them from
+    // here instead of a second sweep over x and dy (b200_gn_param_grad)
+    float* cs_out = a.chan_sums + ((size_t)b * a.nsplit + sp) * C * 2;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) { cs_out[2 * c] = acc[C + c]; cs_out[2 * c + 1] = acc[c]; }
+  }
   for (int g = threadIdx.x; g < a.G; g += blockDim.x) {
     float t1 = 0.f, t2 = 0.f;
-    for (int j = 0; j < cpg; ++j) { t1 += acc[g * cpg + j]; t2 += acc[C + g * cpg + j]; }
+    for (int j = 0; j < cpg; ++j) {
+      const int c = g * cpg + j;
+      const float gc = a.gamma ? a.gamma[c] : 1.0f;
+      t1 = fmaf(gc, acc[c], t1); t2 = fmaf(gc, acc[C + c], t2);
+    }
     float* o = a.part_bwd + (((size_t)b * a.nsplit + sp) * a.G + g) * 2;
     o[0] = t1; o[1] = t2;
   }
@@ -366,24 +381,33 @@ static int gn_bwd_fill(GnBwdArgs& a, const void* x1, int C1, const void* x2, int
   if (C1 % 8 || C2 % 8 || C % G || gn_bwd_threads(C) == 0) return B200_ERR_UNSUPPORTED;
   a.x1 = x1; a.x2 = x2; a.C1 = C1; a.C2 = C2; a.B = B; a.HW = HW; a.G = G; a.nsplit = nsplit;
   a.part_fwd = part_fwd; a.part_bwd = part_bwd; a.gamma = gamma; a.beta = beta; a.eps = eps; a.act = act; a.dy = dy;
-  a.dx1 = nullptr; a.dx2 = nullptr; a.acc1 = 0; a.acc2 = 0;
+  a.dx1 = nullptr; a.dx2 = nullptr; a.acc1 = 0; a.acc2 = 0; a.chan_sums = nullptr;
   return B200_OK;
 }
 
 // Backward of GroupNorm(+SiLU) (models/layers.py:618-642, layerspp.py:243,264): per-(sample, split, group) sums of
 // t = dy act'(z) gamma and t * xhat.  part_fwd comes from b200_gn_partial on the same sources.
-extern "C" int b200_gn_bwd_partial(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G,
-                                   int nsplit, const float* part_fwd, const float* gamma, const float* beta, float eps,
-                                   int act, const void* dy, float* part_bwd, cudaStream_t st) {
+// chan_sums (may be NULL): [B][nsplit][C1 + C2][2] = (sum dz xhat, sum dz) per channel and block: summed over B and nsplit
+// they are d gamma / d beta (the training plans' GroupNorm parameter gradients, at no extra pass)
+extern "C" int b200_gn_bwd_partial2(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G,
+                                    int nsplit, const float* part_fwd, const float* gamma, const float* beta, float eps,
+                                    int act, const void* dy, float* part_bwd, float* chan_sums, cudaStream_t st) {
   GnBwdArgs a;
   int rc = gn_bwd_fill(a, x1, C1, x2, C2, B, HW, G, nsplit, part_fwd, part_bwd, gamma, beta, eps, act, dy);
   if (rc || B == 0) return rc;
+  a.chan_sums = chan_sums;
   const int C = C1 + C2, thr = gn_bwd_threads(C);
   const size_t smem = (size_t)2 * G * sizeof(float) + (size_t)(thr / (C / 8)) * 2 * C * sizeof(float);
   if (dtype == B200_DT_F32) gn_bwd_partial_kernel<float><<<B * nsplit, thr, smem, st>>>(a);
   else if (dtype == B200_DT_BF16) gn_bwd_partial_kernel<bf16><<<B * nsplit, thr, smem, st>>>(a);
   else return B200_ERR_ARG;
   B200_RETURN_LAST();
+}
+
+extern "C" int b200_gn_bwd_partial(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G,
+                                   int nsplit, const float* part_fwd, const float* gamma, const float* beta, float eps,
+                                   int act, const void* dy, float* part_bwd, cudaStream_t st) {
+  return b200_gn_bwd_partial2(x1, C1, x2, C2, dtype, B, HW, G, nsplit, part_fwd, gamma, beta, eps, act, dy, part_bwd, nullptr, st);
 }
 
 // dx = rstd (t - mean_g(t) - xhat mean_g(t xhat)), written (acc = 0) or added (acc = 1) to dx1 / dx2 (either may be NULL).

@@ -39,6 +39,8 @@ _lib.register_signature("b200_transpose2d", [c_vp, c_vp, c_int, c_ll, c_int, c_v
 _lib.register_signature("b200_im2col_t", [c_vp, c_int, c_vp, c_int, c_vp, c_int] + [c_int] * 8 + [c_vp])
 _lib.register_signature("b200_sum_partials", [c_vp, c_vp, c_int, c_int, c_ll, c_vp])
 _lib.register_signature("b200_colsum", [c_vp, c_vp, c_int, c_int, c_ll, c_int, c_ll, c_float, c_int, c_vp])
+_lib.register_signature("b200_gn_bwd_partial2", [c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_vp,
+                                                 c_float, c_int, c_vp, c_vp, c_vp, c_vp])
 _lib.register_signature("b200_gn_param_grad", [c_vp, c_int, c_vp, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp,
                                                c_vp, c_float, c_int, c_vp, c_vp])
 _lib.register_signature("b200_gemm_f32", [c_vp, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_float, c_float, c_vp])
@@ -201,16 +203,19 @@ def _gn_bwd(b, G, t):
     ga, be = e.dev(t["key"] + ".weight"), e.dev(t["key"] + ".bias")
     act = 1 if t["act"] else 0
     b.emit("b200_gn_partial", x, x.C, p2, c2, b.dt, b.B, HW, groups, ns, pf.data_ptr())
-    b.emit("b200_gn_bwd_partial", x, x.C, p2, c2, b.dt, b.B, HW, groups, ns, pf.data_ptr(), ga, be, 1e-6, act, gy,
-           pb.data_ptr())
     if getattr(e, "param_grads", False):
+        # d gamma / d beta are sums over the batch of per-channel sums the backward's first sweep forms anyway
+        # (b200_gn_bwd_partial2 leaves them per block); a separate b200_gn_param_grad sweep was 3.7 ms of a C3 step
         C = x.C + c2
-        part = b.f32(b.B * C * 2)
+        part = b.f32(b.B * ns * C * 2)
         gsum = b.f32(C * 2)
-        b.emit("b200_gn_param_grad", x, x.C, p2, c2, gy, b.dt, b.B, HW, groups, ns, pf.data_ptr(), ga, be, 1e-6, act,
-               part.data_ptr())
-        b.emit("b200_colsum", part.data_ptr(), gsum.data_ptr(), 0, 1, b.B, 2 * C, 2 * C, 1.0, 0)
+        b.emit("b200_gn_bwd_partial2", x, x.C, p2, c2, b.dt, b.B, HW, groups, ns, pf.data_ptr(), ga, be, 1e-6, act, gy,
+               pb.data_ptr(), part.data_ptr())
+        b.emit("b200_colsum", part.data_ptr(), gsum.data_ptr(), 0, 1, b.B * ns, 2 * C, 2 * C, 1.0, 0)
         b.plan.pgrads.append(dict(kind="gn", key=t["key"], buf=gsum, C=C))
+    else:
+        b.emit("b200_gn_bwd_partial", x, x.C, p2, c2, b.dt, b.B, HW, groups, ns, pf.data_ptr(), ga, be, 1e-6, act, gy,
+               pb.data_ptr())
     g1, a1 = G.target(x)
     g2, a2 = G.target(x2) if x2 is not None else (None, 0)
     b.emit("b200_gn_bwd_apply", x, x.C, p2, c2, b.dt, b.B, HW, groups, ns, pf.data_ptr(), pb.data_ptr(), ga, be, 1e-6,

@@ -376,8 +376,9 @@ def other_config_measurements(dev, timeit):
         res["C3_training_step"] = {"batch": Bt, "ms_per_step": ms, "images_per_s": Bt / ms * 1e3, "loss_first": l0,
                                    "loss_last": float(tr.loss[0]), "launches": len(tr.plan.ops),
                                    "parameters": tr.n, "finite": bool(torch.isfinite(tr.flat_p).all()),
-                                   "note": "weight gradients on b200_conv2d_tc over K = pixels; gradient "
-                                           "collection and weight re-packing are one b200_copy_batch launch each"}
+                                   "note": "weight gradients: b200_wgrad_tc (split-K over pixels, MN-major "
+                                           "operands, no im2col); gradient collection and weight re-packing: one "
+                                           "b200_copy_batch launch each"}
         del mt, state, tr
         torch.cuda.empty_cache()
     except Exception as e:  # noqa: BLE001

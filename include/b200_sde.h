@@ -248,6 +248,11 @@ int b200_grid_sample_grad2(int dim, float* gg_out, float* g_in, float* g_grid, c
 int b200_gn_bwd_partial(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G, int nsplit,
                         const float* part_fwd, const float* gamma, const float* beta, float eps, int act, const void* dy,
                         float* part_bwd, cudaStream_t stream);
+/* the same pass, also leaving the per-channel sums chan_sums[B][nsplit][C][2] = (sum dz xhat, sum dz): summed over B and
+ * nsplit they are d gamma / d beta (loss.backward() on nn.GroupNorm's affine parameters, losses.py:196) */
+int b200_gn_bwd_partial2(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G, int nsplit,
+                         const float* part_fwd, const float* gamma, const float* beta, float eps, int act,
+                         const void* dy, float* part_bwd, float* chan_sums, cudaStream_t stream);
 int b200_gn_bwd_apply(const void* x1, int C1, const void* x2, int C2, int dtype, int B, int HW, int G, int nsplit,
                       const float* part_fwd, const float* part_bwd, const float* gamma, const float* beta, float eps,
                       int act, const void* dy, void* dx1, int acc1, void* dx2, int acc2, cudaStream_t stream);
