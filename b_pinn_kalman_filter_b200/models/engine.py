@@ -518,6 +518,8 @@ class ScoreEngine:
         self.params.update(new)
         self._packed.clear()
         self._recipes.clear()
+        self._splits.clear()
+        self._refresh_cl = None
         self._dev.clear()
         self.plans.clear()
         self.graphs.clear()

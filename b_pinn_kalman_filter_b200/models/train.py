@@ -67,7 +67,7 @@ class Trainer:
         self.flat_ema = self.flat_p.clone()
         self.ema_views = {k: self.flat_ema[self.offsets[k]:self.offsets[k] + self.views[k].numel()].view(shapes[k])
                           for k in self.keys}
-        eng._packed.clear(); eng._recipes.clear(); eng.plans.clear(); eng.graphs.clear()
+        eng._packed.clear(); eng._recipes.clear(); eng._splits.clear(); eng._refresh_cl = None; eng.plans.clear(); eng.graphs.clear()
         eng.workspace = Workspace(self.dev)
         eng.version += 1
         # ---- training plan ----
