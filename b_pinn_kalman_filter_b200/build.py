@@ -14,7 +14,8 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libb200sde.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-         "-Xcompiler", "-fPIC", "-DB200_BUILDING"]
+         "-Xcompiler", "-fPIC", "-DB200_BUILDING"] + os.environ.get("B200_NVCC_EXTRA", "").split()
+# B200_NVCC_EXTRA: extra nvcc flags for profiling builds (e.g. -DB200_ATTN_TRACE, see profiles/prof_attn_phases.py)
 # No --use_fast_math: fp32 parity (1e-5) needs IEEE div/sqrt and accurate sin/cos/log; hot loops use explicit
 # intrinsics (__expf, __sincosf) where the error budget allows.
 PRECISE = set()

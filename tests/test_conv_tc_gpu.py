@@ -92,7 +92,7 @@ def test_conv_tc_unsupported_shapes_are_refused(cuda):
     assert lib.b200_conv2d_tc_supported(128, 0, 4, 24, 24, 128, 3, 1, 0) == 0    # 128 % W != 0
 
 
-@pytest.mark.parametrize("B", [1, 3, 150])
+@pytest.mark.parametrize("B", [1, 3, 150, 75, 520])     # 2 ... 1040 tiles: 1 to 8 per persistent CTA, odd and even
 def test_attention_tc_matches_torch_fp32(cuda, B):
     from b_pinn_kalman_filter_b200 import _lib
     from b_pinn_kalman_filter_b200.models import tc  # noqa: F401
