@@ -177,89 +177,183 @@ __global__ void __launch_bounds__(256) upfirdn2d_nhwc_kernel(const T* __restrict
 
 // Channels-last 4x4-filter variant, register blocked: one thread = 8 channels of a 2x2 block of output pixels.  Each
 // input vector of the (WIN x WIN) window is loaded once and scattered into the outputs it feeds, which cuts the loads
-// per output from 16 to 9 (down 2), 2.25 (up 2) and 6.25 (pad-only) and keeps the kernel on the HBM roofline instead
-// of the L1 one.
-// PAD0 is a template parameter: with even block origins the tap index of window row wy is PAD0 % UP + wy * UP, a
-// compile-time number, so every "does this tap exist" test folds away (the runtime-pad version spent 66 branches and
-// 2.25x the necessary FMAs per thread on them and ran at 25 % of HBM for the up-2 shape).
-// NA = output rows per thread (x 2 columns): 2 for the up-2 shape (3 x 3 window), 1 for down-2 / pad-only, whose
-// 6 x 6 / 5 x 5 windows for two rows cost > 140 registers once the taps are static.
-template <typename T, int UP, int DOWN, int PAD0, int NA>
-__global__ void __launch_bounds__(256) upfirdn2d_nhwc4_kernel(const T* __restrict__ in, const float* __restrict__ k,
-                                                              T* __restrict__ out, long long total, int C8, int in_h,
-                                                              int in_w, int out_h, int out_w, int pad0_rt) {
-  static_assert(UP == 1 || NA == 2, "odd block origins need UP == 1");
-  // PAD0 < 0: padding (and with it the tap pattern) is a runtime value -- measured faster for the 6 x 6 / 5 x 5
-  // windows of down-2 / pad-only (3.4 / 1.9 TB/s vs 2.0 / 1.1 with static taps, which cost 140+ registers)
-  const int pad0 = PAD0 >= 0 ? PAD0 : pad0_rt;
-  constexpr int K0 = PAD0 >= 0 ? PAD0 % UP : 0;
-  constexpr int WINY = ((NA - 1) * DOWN + 3) / UP + 1;
-  constexpr int WIN = (DOWN + 3) / UP + 1;      // input rows/cols that can touch a 2-wide output block
-  __shared__ float sk[16];
-  if (threadIdx.x < 16) sk[threadIdx.x] = k[(3 - (threadIdx.x >> 2)) * 4 + (3 - (threadIdx.x & 3))];   // flipped taps
-  __syncthreads();
-  const int bw = (out_w + 1) >> 1, bh = (out_h + NA - 1) / NA;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    long long r = i / C8;
-    const int ox0 = (int)(r % bw) * 2; r /= bw;
-    const int oy0 = (int)(r % bh) * NA;
-    const long long b = r / bh;
-    const T* ip = in + b * (long long)in_h * in_w * C8 * 8 + c8 * 8;
-    const int uy0 = oy0 * DOWN - pad0, ux0 = ox0 * DOWN - pad0;       // upsampled-grid coordinate of tap (0, 0)
-    const int iy0 = floor_div(uy0 + UP - 1, UP), ix0 = floor_div(ux0 + UP - 1, UP);
-    float acc[NA][2][8];
+// per output from 16 to 9 (down 2), 2.25 (up 2) and 6.25 (pad-only).
+// The kernel is bound by instruction issue and by loads in flight, not by bytes, so those are what was engineered
+// (ncu source page of the first version, up-2 shape: 639 instructions per thread of which 128 FFMA, 171 IMAD, 54 IADD3,
+// 50 SHF, 46 ISETP -- profiles/r02o_fir.txt):
+//   * the padding is a template parameter: with even block origins the COLUMN tap of window column wx for output
+//     column c is K0 + wx * UP - c * DOWN, a compile-time number; rows are a real loop for UP == 1 (one window row of
+//     16/32-byte loads in flight, bounded registers) with one uniform test + one 32-byte tap-row fetch per (row,
+//     output row);
+//   * index arithmetic is 32-bit: the thread index is decomposed with host-computed multiply-shift divisors (a shift
+//     when the channel count is one of the templated 128 / 256 / 512), and every load address is ONE per-thread
+//     64-bit window origin + a row offset + a column offset that is an immediate for the templated channel counts.
+//     The loads are inline PTX (`@p ld.global.nc.v4` after zeroing the destination) because the compiler otherwise
+//     sinks the whole address computation under each load's predicate: 9-10 instructions per load;
+//   * the accumulation is packed: fma.rn.f32x2 (FFMA2) on channel pairs -- the same IEEE fma per lane, half the issue
+//     slots; a bf16 pair unpacks into exactly such a register pair with two ALU ops;
+//   * MINB = 3 (<= 80 registers, 24 warps per SM) for the bf16 shapes: the UP == 1 loops have one window row in
+//     flight per warp and need the warps (down-2 3.7 -> 4.4 TB/s; a two-row software pipeline at 124 registers gave
+//     the same and nothing on top).
+// B = 1024, bf16: up-2 16x16x256 216 -> 127 us (5.3 TB/s, 0.81 of HBM), down-2 32x32x128 97 -> 70 us (4.8 TB/s, 0.73),
+// pad-only 16x16x256 161 -> 111 us (2.6 TB/s: 16 taps per output at stride 1, still issue-bound).
+struct FastDiv {
+  uint32_t d, mul, shr;   // n / d == umulhi(n, mul) >> shr for n < 2^31 (d >= 2); d == 1 is passed through
+};
+static inline FastDiv make_fastdiv(uint32_t d) {
+  FastDiv f{d, 0u, 0u};
+  if (d <= 1) return f;
+  uint32_t s = 0;
+  while ((1ull << s) < d) ++s;                                  // ceil(log2 d)
+  f.mul = (uint32_t)(((1ull << (31 + s)) + d - 1) / d);         // ceil(2^(31+s) / d) < 2^32
+  f.shr = s - 1;
+  return f;
+}
+__device__ __forceinline__ uint32_t fd_div(uint32_t n, const FastDiv& f) {
+  return f.d == 1 ? n : (__umulhi(n, f.mul) >> f.shr);
+}
+__device__ __forceinline__ void ffma2(float2& acc, const float2 v, const float2 w) {
+  unsigned long long a = *reinterpret_cast<unsigned long long*>(&acc);
+  const unsigned long long x = *reinterpret_cast<const unsigned long long*>(&v),
+                           y = *reinterpret_cast<const unsigned long long*>(&w);
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(a) : "l"(x), "l"(y));
+  acc = *reinterpret_cast<float2*>(&a);
+}
+// eight channels as loaded (no conversion), and channel pair p of them as a float2
+template <typename T> struct Raw8;
+template <> struct Raw8<float> {
+  float4 lo, hi;
+  static __device__ __forceinline__ Raw8 load(const float* p) {
+    Raw8 r; r.lo = *reinterpret_cast<const float4*>(p); r.hi = *reinterpret_cast<const float4*>(p + 4); return r;
+  }
+  static __device__ __forceinline__ Raw8 zero() { Raw8 r; r.lo = r.hi = make_float4(0.f, 0.f, 0.f, 0.f); return r; }
+  // eight channels at byte address p + off when ok, zeros otherwise; the address is formed unconditionally
+  static __device__ __forceinline__ Raw8 load_if(const char* p, int off, int ok) {
+    Raw8 r;
+    asm("{\n .reg .pred q;\n setp.ne.s32 q, %9, 0;\n"
+        " mov.b32 %0, 0; mov.b32 %1, 0; mov.b32 %2, 0; mov.b32 %3, 0; mov.b32 %4, 0; mov.b32 %5, 0; mov.b32 %6, 0; mov.b32 %7, 0;\n"
+        " @q ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%8];\n @q ld.global.nc.v4.f32 {%4, %5, %6, %7}, [%8+16];\n}"
+        : "=f"(r.lo.x), "=f"(r.lo.y), "=f"(r.lo.z), "=f"(r.lo.w), "=f"(r.hi.x), "=f"(r.hi.y), "=f"(r.hi.z), "=f"(r.hi.w)
+        : "l"(p + off), "r"(ok));
+    return r;
+  }
+  __device__ __forceinline__ float2 pair(int p) const {
+    return p == 0 ? make_float2(lo.x, lo.y) : p == 1 ? make_float2(lo.z, lo.w) : p == 2 ? make_float2(hi.x, hi.y)
+                                                                                       : make_float2(hi.z, hi.w);
+  }
+  static __device__ __forceinline__ void store(float* p, const float2* v) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0].x, v[0].y, v[1].x, v[1].y);
+    *reinterpret_cast<float4*>(p + 4) = make_float4(v[2].x, v[2].y, v[3].x, v[3].y);
+  }
+};
+template <> struct Raw8<bf16> {
+  uint4 w;
+  static __device__ __forceinline__ Raw8 load(const bf16* p) { Raw8 r; r.w = *reinterpret_cast<const uint4*>(p); return r; }
+  static __device__ __forceinline__ Raw8 zero() { Raw8 r; r.w = make_uint4(0u, 0u, 0u, 0u); return r; }
+  static __device__ __forceinline__ Raw8 load_if(const char* p, int off, int ok) {
+    Raw8 r;
+    asm("{\n .reg .pred q;\n setp.ne.s32 q, %5, 0;\n mov.b32 %0, 0; mov.b32 %1, 0; mov.b32 %2, 0; mov.b32 %3, 0;\n"
+        " @q ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];\n}"
+        : "=r"(r.w.x), "=r"(r.w.y), "=r"(r.w.z), "=r"(r.w.w)
+        : "l"(p + off), "r"(ok));
+    return r;
+  }
+  __device__ __forceinline__ float2 pair(int p) const {
+    const uint32_t x = p == 0 ? w.x : p == 1 ? w.y : p == 2 ? w.z : w.w;
+    return make_float2(__uint_as_float(x << 16), __uint_as_float(x & 0xffff0000u));
+  }
+  static __device__ __forceinline__ void store(bf16* p, const float2* v) {
+    uint4 r;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
 #pragma unroll
-    for (int a = 0; a < NA; ++a)
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[i].x, v[i].y);
+    *reinterpret_cast<uint4*>(p) = r;
+  }
+};
+
+template <typename T, int UP, int DOWN, int PAD0, int MINB, int C8T>
+__global__ void __launch_bounds__(256, MINB) upfirdn2d_nhwc4_kernel(const T* __restrict__ in, const float* __restrict__ k,
+                                                              T* __restrict__ out, uint32_t total, FastDiv dC8,
+                                                              FastDiv dbw, FastDiv dbh, int in_h, int in_w, int out_h,
+                                                              int out_w) {
+  static_assert(UP == 1 || (UP == 2 && DOWN == 1), "block origins are even: UP in {1, 2}");
+  constexpr int K0 = PAD0 % UP;
+  constexpr int WIN = (DOWN + 3) / UP + 1;      // input rows / cols that can touch a 2-wide output block
+  __shared__ float2 skp[16];                    // flipped taps, each duplicated into an FFMA2 operand pair
+  if (threadIdx.x < 16) {
+    const float w = k[(3 - (threadIdx.x >> 2)) * 4 + (3 - (threadIdx.x & 3))];
+    skp[threadIdx.x] = make_float2(w, w);
+  }
+  __syncthreads();
+  // C8T != 0: the channel count is a compile-time number (a power of two): column offsets become load immediates and
+  // the first division a shift
+  const uint32_t C8 = C8T ? (uint32_t)C8T : dC8.d;
+  const int C = (int)C8 * 8;
+  // everything below is int arithmetic on element offsets inside ONE image (the host guarantees < 2^31); the only
+  // 64-bit operations are the per-image base and one widening add per load / store
+  const int rowstride = in_w * C, in_img = in_h * rowstride;
+  const int orow = out_w * C, out_img = out_h * orow;
+  for (uint32_t i = blockIdx.x * 256u + threadIdx.x; i < total; i += gridDim.x * 256u) {
+    const uint32_t r1 = C8T ? i / (uint32_t)(C8T ? C8T : 1) : fd_div(i, dC8), c8 = i - r1 * C8;
+    const uint32_t r2 = fd_div(r1, dbw);
+    const int ox0 = (int)(r1 - r2 * dbw.d) * 2;
+    const uint32_t b = fd_div(r2, dbh);
+    const int oy0 = (int)(r2 - b * dbh.d) * 2;
+    const int uy0 = oy0 * DOWN - PAD0, ux0 = ox0 * DOWN - PAD0;       // upsampled-grid coordinate of tap (0, 0)
+    const int iy0 = UP == 1 ? uy0 : ((uy0 + 1) >> 1), ix0 = UP == 1 ? ux0 : ((ux0 + 1) >> 1);
+    // byte address of the window origin (may lie outside the image: never dereferenced there)
+    const char* p00 = reinterpret_cast<const char*>(in + (size_t)b * (uint32_t)in_img + c8 * 8) +
+                      (long long)(iy0 * rowstride + ix0 * C) * (int)sizeof(T);
+    int colok[WIN];
+#pragma unroll
+    for (int wx = 0; wx < WIN; ++wx) colok[wx] = (unsigned)(ix0 + wx) < (unsigned)in_w;
+    float2 acc[2][2][4];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
 #pragma unroll
       for (int c = 0; c < 2; ++c)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[a][c][j] = 0.0f;
-    // NA == 1: rows stay a real loop (6 loads in flight, ~60 registers); fully unrolled the compiler hoists all 24
-    // loads and needs 146 registers.  NA == 2 (3 x 3 window) is small enough to unroll.
-#pragma unroll(NA == 1 ? 1 : WINY)
-    for (int wy = 0; wy < WINY; ++wy) {
-      const int iy = iy0 + wy;
-      const bool row_ok = iy >= 0 && iy < in_h;
-      const int ky_a = PAD0 >= 0 ? K0 + wy * UP : iy * UP - uy0;       // tap row for output row oy0 (-DOWN per row)
-      // the whole window row is requested before any of it is used (no control flow between the loads): WIN
-      // independent 16/32-byte loads in flight per thread instead of one
-      float v[WIN][8];
+        for (int p = 0; p < 4; ++p) acc[a][c][p] = make_float2(0.f, 0.f);
+    auto load_row = [&](int wy, Raw8<T>* v) {                       // the whole window row is requested at once
+      const int row_ok = (unsigned)(iy0 + wy) < (unsigned)in_h;
+      const char* rp = p00 + (long long)(wy * rowstride) * (int)sizeof(T);
 #pragma unroll
-      for (int wx = 0; wx < WIN; ++wx) {
-        const int ix = ix0 + wx;
-        if (row_ok && ix >= 0 && ix < in_w) Vec8<T>::load(ip + ((long long)iy * in_w + ix) * C8 * 8, v[wx]);
-        else {
+      for (int wx = 0; wx < WIN; ++wx) v[wx] = Raw8<T>::load_if(rp, wx * C * (int)sizeof(T), row_ok & colok[wx]);
+    };
+    auto use_row = [&](int wy, const Raw8<T>* v) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) v[wx][j] = 0.0f;
-        }
-      }
+      for (int a = 0; a < 2; ++a) {
+        const int ky = K0 + wy * UP - a * DOWN;                      // uniform over the block; static when unrolled
+        if ((unsigned)ky >= 4u) continue;
+        float2 wrow[4];
+        *reinterpret_cast<float4*>(&wrow[0]) = *reinterpret_cast<const float4*>(&skp[ky * 4]);
+        *reinterpret_cast<float4*>(&wrow[2]) = *reinterpret_cast<const float4*>(&skp[ky * 4 + 2]);
 #pragma unroll
-      for (int wx = 0; wx < WIN; ++wx) {
-        const int kx_a = PAD0 >= 0 ? K0 + wx * UP : (ix0 + wx) * UP - ux0;
-#pragma unroll
-        for (int a = 0; a < NA; ++a) {
-          const int ky = ky_a - a * DOWN;
-          if ((unsigned)ky >= 4u) continue;
+        for (int wx = 0; wx < WIN; ++wx)
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
-            const int kx = kx_a - c * DOWN;
-            if ((unsigned)kx >= 4u) continue;
-            const float wk = sk[ky * 4 + kx];
+            const int kx = K0 + wx * UP - c * DOWN;                  // compile-time
+            if (kx < 0 || kx >= 4) continue;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) acc[a][c][j] = fmaf(v[wx][j], wk, acc[a][c][j]);
+            for (int p = 0; p < 4; ++p) ffma2(acc[a][c][p], v[wx].pair(p), wrow[kx]);
           }
-        }
       }
+    };
+    // UP == 1: rows stay a real loop (unrolled, the compiler hoists all 25-36 loads and needs 140+ registers).
+    // UP == 2 (3 x 3 window) is small enough to unroll.
+#pragma unroll(UP == 1 ? 1 : WIN)
+    for (int wy = 0; wy < WIN; ++wy) {
+      Raw8<T> v[WIN];
+      load_row(wy, v);
+      use_row(wy, v);
     }
-#pragma unroll
-    for (int a = 0; a < NA; ++a)
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        const int oy = oy0 + a, ox = ox0 + c;
-        if (oy < out_h && ox < out_w)
-          Vec8<T>::store(out + ((b * out_h + oy) * (long long)out_w + ox) * C8 * 8 + c8 * 8, acc[a][c]);
-      }
+    T* op = out + (size_t)b * (uint32_t)out_img + c8 * 8;
+    const int o00 = oy0 * orow + ox0 * C;
+    const bool ok_y1 = oy0 + 1 < out_h, ok_x1 = ox0 + 1 < out_w;      // (oy0, ox0) itself always exists
+    Raw8<T>::store(op + o00, acc[0][0]);
+    if (ok_x1) Raw8<T>::store(op + (o00 + C), acc[0][1]);
+    if (ok_y1) Raw8<T>::store(op + (o00 + orow), acc[1][0]);
+    if (ok_y1 && ok_x1) Raw8<T>::store(op + (o00 + orow + C), acc[1][1]);
   }
 }
 
@@ -459,21 +553,33 @@ extern "C" int b200_upfirdn2d_nhwc(const void* in, const float* k, void* out, in
   if (out_h <= 0 || out_w <= 0) return B200_ERR_ARG;
   long long total = (long long)batch * out_h * out_w * (channels / 8);
   if (total == 0) return B200_OK;
-  const int mode = (kh == 4 && kw == 4) ? ((up == 2 && down == 1 && pad0 == 2) ? 1 : (up == 1 && down == 2) ? 2
-                                                        : (up == 1 && down == 1) ? 3 : 0) : 0;
-  if (mode) {
-    const int na = 2;
-    const long long tot4 = (long long)batch * ((out_h + na - 1) / na) * ((out_w + 1) / 2) * (channels / 8);
+  // register-blocked kernel for the three shapes the score networks use (up_or_down_sampling.py:195-257 and
+  // conv_downsample_2d :144-178): up 2 / pad (2,1), down 2 / pad (1,1), pad-only / pad (2,2)
+  const int mode = (kh == 4 && kw == 4) ? ((up == 2 && down == 1 && pad0 == 2) ? 1 : (up == 1 && down == 2 && pad0 == 1) ? 2
+                                                        : (up == 1 && down == 1 && pad0 == 2) ? 3 : 0) : 0;
+  const long long tot4 = (long long)batch * ((out_h + 1) / 2) * ((out_w + 1) / 2) * (channels / 8);
+  if (mode && tot4 < (1ll << 31) && (long long)in_h * in_w * channels < (1ll << 31) &&
+      (long long)out_h * out_w * channels < (1ll << 31)) {
     long long w4 = (tot4 + 255) / 256;
     const int blk = (int)(w4 < (long long)B200_NUM_SMS * 32 ? w4 : (long long)B200_NUM_SMS * 32);
-#define B200_UFD4(T, U, D, P0, NA) upfirdn2d_nhwc4_kernel<T, U, D, P0, NA><<<blk, 256, 0, st>>>((const T*)in, k, (T*)out, tot4, channels / 8, in_h, in_w, out_h, out_w, pad0)
+    const FastDiv dC8 = make_fastdiv((uint32_t)(channels / 8)), dbw = make_fastdiv((uint32_t)((out_w + 1) / 2)),
+                  dbh = make_fastdiv((uint32_t)((out_h + 1) / 2));
+#define B200_UFD4(T, U, D, P0, MB, CT) upfirdn2d_nhwc4_kernel<T, U, D, P0, MB, CT><<<blk, 256, 0, st>>>((const T*)in, k, (T*)out, (uint32_t)tot4, dC8, dbw, dbh, in_h, in_w, out_h, out_w)
+#define B200_UFD4_C(T, U, D, P0, MB)                                                       \
+  do {                                                                                     \
+    if (channels == 128) B200_UFD4(T, U, D, P0, MB, 16);                                    \
+    else if (channels == 256) B200_UFD4(T, U, D, P0, MB, 32);                               \
+    else if (channels == 512) B200_UFD4(T, U, D, P0, MB, 64);                               \
+    else B200_UFD4(T, U, D, P0, MB, 0);                                                     \
+  } while (0)
     if (dtype == B200_DT_F32) {
-      if (mode == 1) B200_UFD4(float, 2, 1, 2, 2); else if (mode == 2) B200_UFD4(float, 1, 2, -1, 2); else B200_UFD4(float, 1, 1, -1, 2);
+      if (mode == 1) B200_UFD4(float, 2, 1, 2, 2, 0); else if (mode == 2) B200_UFD4(float, 1, 2, 1, 2, 0); else B200_UFD4(float, 1, 1, 2, 2, 0);
     } else if (dtype == B200_DT_BF16) {
-      if (mode == 1) B200_UFD4(bf16, 2, 1, 2, 2); else if (mode == 2) B200_UFD4(bf16, 1, 2, -1, 2); else B200_UFD4(bf16, 1, 1, -1, 2);
+      if (mode == 1) B200_UFD4_C(bf16, 2, 1, 2, 3); else if (mode == 2) B200_UFD4_C(bf16, 1, 2, 1, 3); else B200_UFD4_C(bf16, 1, 1, 2, 3);
     } else {
       return B200_ERR_ARG;
     }
+#undef B200_UFD4_C
 #undef B200_UFD4
     B200_RETURN_LAST();
   }

@@ -65,7 +65,12 @@ def test_groupnorm_silu(cuda, dtype, B, HW, C1, C2, G):
                                                 (2, 8, 8, 256, 1, 1, (2, 2)), (1, 64, 64, 128, 1, 2, (1, 1)),
                                                 # more up-2 shapes: one block row, ragged extents, C = 64
                                                 (2, 8, 8, 128, 2, 1, (2, 1)), (2, 20, 20, 64, 2, 1, (2, 1)),
-                                                (1, 128, 128, 64, 2, 1, (2, 1))])
+                                                (1, 128, 128, 64, 2, 1, (2, 1)),
+                                                # non-square, C / 8 = 48 (not a power of two), odd extents
+                                                (2, 10, 6, 384, 1, 2, (1, 1)), (2, 6, 10, 384, 2, 1, (2, 1)),
+                                                (2, 7, 9, 64, 1, 1, (2, 2)), (3, 5, 5, 8, 1, 2, (1, 1)),
+                                                # other paddings take the generic kernel
+                                                (2, 8, 8, 64, 1, 2, (2, 2)), (2, 8, 8, 64, 2, 1, (1, 1))])
 def test_upfirdn2d_nhwc(cuda, dtype, B, H, W, C, up, down, pad):
     L = _lib()
     rng = np.random.default_rng(H + C)
