@@ -16,6 +16,7 @@ _lib.register_signature("b200_gn_apply_stats", [c_vp, c_int, c_vp, c_int, c_vp, 
                                                 c_int, c_int, c_vp, c_vp, c_float, c_int, c_vp, c_vp])
 
 _lib.register_signature("b200_gn_fold_stats", [c_vp, c_vp, c_int, c_int, c_int, c_vp])
+_lib.register_signature("b200_gn_small_enable", [c_int])
 _lib.register_signature("b200_gn_coef", [c_vp, c_int, c_int, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp, c_float,
                                         c_vp])
 _lib.register_signature("b200_conv2d_tc_gn_supported", [c_int] * 7)

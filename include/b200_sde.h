@@ -127,6 +127,10 @@ int b200_gn_apply(const void* x1, int C1, const void* x2, int C2, int dtype, int
 int b200_gn_apply_stats(const void* x1, int C1, const float* st1, int T1, const void* x2, int C2, const float* st2,
                         int T2, int dtype, int B, int HW, int G, int nsplit, const float* gamma, const float* beta,
                         float eps, int act, void* out, cudaStream_t stream);
+/* b200_gn_apply_stats uses a thread-per-group kernel (no shared memory, no barrier; bit-identical output) for images of
+ * at most 64 pixels with at most 4 statistics slots.  on = 0 switches it off (A/B measurements, bit-identity tests);
+ * returns the previous setting.  Not a reference interface. */
+int b200_gn_small_enable(int on);
 /* layout changes at the API boundary (NCHW fp32 <-> channels-last), incl. `2x-1` (ncsnpp.py:261) and `h/sigma` (:379) */
 int b200_nchw_to_nhwc(const float* x, void* out, int dtype, int B, int C, int H, int W, int Cp, float scale,
                       float shift, cudaStream_t stream);

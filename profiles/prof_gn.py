@@ -55,3 +55,8 @@ def graph_us(fn, n=40):
 for nsv in [int(v) for v in os.environ.get("NS_LIST", str(ns)).split(",")]:
     us = graph_us(lambda st_: lib.b200_gn_apply_stats(P(x), C, P(st), T, None, 0, None, 0, 1, B, HW, G, nsv, P(gamma), P(beta), 1e-6, 1, P(out), st_))
     print("graph: gn_apply_stats B=%d HW=%d C=%d ns=%d: %.2f us  %.0f GB/s" % (B, HW, C, nsv, us, nbytes / us / 1e3))
+if HW <= 64:     # thread-per-group kernel (default) against the block-per-image kernel
+    lib.b200_gn_small_enable(0)
+    us = graph_us(lambda st_: lib.b200_gn_apply_stats(P(x), C, P(st), T, None, 0, None, 0, 1, B, HW, G, ns, P(gamma), P(beta), 1e-6, 1, P(out), st_))
+    lib.b200_gn_small_enable(1)
+    print("graph: block-per-image kernel        ns=%d: %.2f us  %.0f GB/s" % (ns, us, nbytes / us / 1e3))

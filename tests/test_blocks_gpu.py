@@ -60,6 +60,52 @@ def test_groupnorm_silu(cuda, dtype, B, HW, C1, C2, G):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,HW,C1,C2,G,T1,T2", [(5, 16, 256, 0, 32, 1, 0), (3, 64, 256, 256, 32, 1, 1), (2, 64, 128, 0, 32, 2, 0),
+                                               (3, 49, 256, 128, 32, 1, 2), (2, 16, 512, 0, 32, 4, 0),
+                                               (300, 16, 256, 0, 32, 1, 0)])
+@pytest.mark.parametrize("act", [0, 1])
+def test_groupnorm_from_statistics_small_images(cuda, dtype, B, HW, C1, C2, G, T1, T2, act):
+    """b200_gn_apply_stats on images of <= 64 pixels takes the thread-per-group kernel: its output must be
+    BIT-identical with the block-per-image kernel's (same sums in the same order) and match torch's group_norm on
+    statistics that are exact for the input."""
+    L = _lib()
+    from b_pinn_kalman_filter_b200.models import tc  # noqa: F401  (registers the signatures)
+    lib = L.lib()
+    g = torch.Generator(device="cpu").manual_seed(HW + C1 + C2 + T1)
+    C = C1 + C2
+    xs = [(torch.randn(B, HW, c, generator=g) * 1.5 + 0.3).to(cuda, dtype) for c in (C1, C2) if c]
+
+    def stats(x, T):                       # [B][T][c][2]: the image's (sum, sum of squares) spread over T slots
+        xf = x.float()
+        parts = xf.tensor_split(T, dim=1)
+        return torch.stack([torch.stack([p.sum(1), (p * p).sum(1)], -1) for p in parts], 1).contiguous()
+    sts = [stats(x, T) for x, T in zip(xs, (T1, T2))]
+    gamma = torch.randn(C, generator=g).to(cuda)
+    beta = torch.randn(C, generator=g).to(cuda)
+    outs = []
+    for small in (1, 0):
+        lib.b200_gn_small_enable(small)
+        try:
+            out = torch.full((B, HW, C), float("nan"), device=cuda, dtype=dtype)
+            x2, s2 = (xs[1], sts[1]) if C2 else (None, None)
+            L.check(lib.b200_gn_apply_stats(L.ptr(xs[0]), C1, L.ptr(sts[0]), T1, L.ptr(x2) if C2 else None, C2,
+                                            L.ptr(s2) if C2 else None, T2, 0 if dtype == torch.float32 else 1, B, HW, G,
+                                            1, L.ptr(gamma), L.ptr(beta), 1e-6, act, L.ptr(out), L.stream()), "gn_apply_stats")
+            torch.cuda.synchronize()
+            outs.append(out)
+        finally:
+            lib.b200_gn_small_enable(1)
+    assert torch.isfinite(outs[0].float()).all()
+    assert torch.equal(outs[0], outs[1])
+    xx = torch.cat(xs, -1)
+    ref = torch.nn.functional.group_norm(xx.double().permute(0, 2, 1), G, gamma.double(), beta.double(), eps=1e-6)
+    ref = ref.permute(0, 2, 1)
+    ref = torch.nn.functional.silu(ref) if act else ref
+    tol = 2e-5 if dtype == torch.float32 else 2 ** -7
+    assert (outs[0].double() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("B,H,W,C,up,down,pad", [(2, 32, 32, 128, 1, 2, (1, 1)), (2, 4, 4, 256, 2, 1, (2, 1)),
                                                 (3, 16, 16, 256, 2, 1, (2, 1)), (2, 32, 32, 8, 1, 1, (2, 2)),
                                                 (2, 8, 8, 256, 1, 1, (2, 2)), (1, 64, 64, 128, 1, 2, (1, 1)),

@@ -127,3 +127,33 @@ def test_network_with_and_without_gn_fusion_is_bit_identical(cuda, B):
     assert gn1 == gn0 - f1, counts              # every fused conv removed its GroupNorm launch
     if B == 2:      # and the fused plan still reproduces the reference's golden output
         assert cases.rel_l2(m(x.to(cuda), labels.to(cuda)).cpu(), out) < 2e-2
+
+
+@pytest.mark.parametrize("B,HW,C1,C2,G,T1,T2", [(3, 1024, 256, 0, 32, 8, 0), (300, 256, 256, 256, 32, 2, 2),
+                                               (2, 1024, 128, 0, 32, 16, 0), (2, 64, 256, 128, 32, 1, 1)])
+def test_gn_coef_thread_per_group_kernel_is_bit_identical(cuda, B, HW, C1, C2, G, T1, T2):
+    """b200_gn_coef takes a thread-per-(image, 8 channels) kernel for <= 16 statistics slots: the same sums in the
+    same order as the block kernel, so the coefficients must be the same bits."""
+    from b_pinn_kalman_filter_b200 import _lib
+    from b_pinn_kalman_filter_b200.models import tc  # noqa: F401
+    lib = _lib.lib()
+    g = torch.Generator(device="cpu").manual_seed(HW + C1 + T1)
+    C = C1 + C2
+    sts = [(torch.rand(B, T, c, 2, generator=g) * 50 + 1).to(cuda) for c, T in ((C1, T1), (C2, T2)) if c]
+    for s in sts:
+        s[..., 1] = s[..., 0] ** 2 / (HW / s.shape[1]) * 1.5 + 1.0          # keeps the variance positive
+    gamma = torch.randn(C, generator=g).to(cuda)
+    beta = torch.randn(C, generator=g).to(cuda)
+    outs = []
+    for small in (1, 0):
+        lib.b200_gn_small_enable(small)
+        try:
+            coef = torch.full((B, C, 2), float("nan"), device=cuda)
+            _lib.check(lib.b200_gn_coef(_lib.ptr(sts[0]), T1, C1, _lib.ptr(sts[1]) if C2 else None, T2, C2, B, HW, G,
+                                        _lib.ptr(gamma), _lib.ptr(beta), 1e-6, _lib.ptr(coef), _lib.stream()), "gn_coef")
+            torch.cuda.synchronize()
+            outs.append(coef)
+        finally:
+            lib.b200_gn_small_enable(1)
+    assert torch.isfinite(outs[0]).all()
+    assert torch.equal(outs[0], outs[1])
