@@ -79,8 +79,12 @@ __global__ void __launch_bounds__(256) gn_partial_kernel(GnArgs a) {
   }
 }
 
-template <typename T>
-__global__ void __launch_bounds__(256) gn_apply_kernel(GnArgs a) {
+// MINB: resident blocks per SM the compiler must allow.  4 (64 registers, a few spilled words in the statistics fold)
+// when the launch is several waves deep -- 1024 one-image blocks stream 4-5 % faster with a fourth block per SM (ncu: 79
+// registers = 3 blocks = 31 % warps active before) -- and 3 (79 registers, no spills) for launches of at most one wave,
+// where the fold's latency is the time and the spills cost 9 % (profiles/r02p_gn_small_images.txt).
+template <typename T, int MINB>
+__global__ void __launch_bounds__(256, MINB) gn_apply_kernel(GnArgs a) {
   extern __shared__ float sh[];  // [G] mean, [G] rstd
   const int C = a.C1 + a.C2, CV = C >> 3;
   const int b = blockIdx.x / a.nsplit, sp = blockIdx.x % a.nsplit;
@@ -387,7 +391,7 @@ static int g_gn_small = 1;
 extern "C" int b200_gn_small_enable(int on) { const int was = g_gn_small; g_gn_small = on ? 1 : 0; return was; }
 
 extern "C" int b200_gn_nsplit(int B, int HW) {
-  // At most ONE wave of blocks (gn_apply_kernel<bf16>: 64 registers x 256 threads = 4 blocks per SM), never fewer than
+  // At most ONE wave of blocks (gn_apply_kernel<bf16>: 256 threads, up to 4 blocks per SM), never fewer than
   // 128 pixels per block: every block folds the image's statistics before it streams (up to 16 slots x C x 8 B), so
   // more, smaller blocks are slower, not faster -- measured inside a CUDA graph (profiles/prof_gn.py, NS_LIST): 128
   // images of 32x32x128: 23.9 us with 10 splits (the old "8 blocks per SM, several waves" rule), 11.4 us = 5.9 TB/s
@@ -437,8 +441,11 @@ extern "C" int b200_gn_apply(const void* x1, int C1, const void* x2, int C2, int
   if (G % 2) return B200_ERR_UNSUPPORTED;              // keeps the double scratch 8-byte aligned
   const size_t smem = 2 * G * sizeof(float) + 2 * C * sizeof(double);
   cudaError_t le;
-  if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float>, dim3(B * nsplit), dim3(thr), smem, st, a);
-  else if (dtype == B200_DT_BF16) le = b200_launch_pdl(gn_apply_kernel<bf16>, dim3(B * nsplit), dim3(thr), smem, st, a);
+  const bool deep = (long long)B * nsplit > (long long)B200_NUM_SMS * 4;      // more than one wave even at 4 blocks per SM
+  if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float, 3>, dim3(B * nsplit), dim3(thr), smem, st, a);
+  else if (dtype == B200_DT_BF16)
+    le = deep ? b200_launch_pdl(gn_apply_kernel<bf16, 4>, dim3(B * nsplit), dim3(thr), smem, st, a)
+              : b200_launch_pdl(gn_apply_kernel<bf16, 3>, dim3(B * nsplit), dim3(thr), smem, st, a);
   else return B200_ERR_ARG;
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
@@ -477,8 +484,11 @@ extern "C" int b200_gn_apply_stats(const void* x1, int C1, const float* st1, int
     B200_RETURN_LAST();
   }
   const size_t smem = 2 * G * sizeof(float) + 2 * C * sizeof(double);
-  if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float>, dim3(B * nsplit), dim3(thr), smem, st, a);
-  else if (dtype == B200_DT_BF16) le = b200_launch_pdl(gn_apply_kernel<bf16>, dim3(B * nsplit), dim3(thr), smem, st, a);
+  const bool deep = (long long)B * nsplit > (long long)B200_NUM_SMS * 4;      // more than one wave even at 4 blocks per SM
+  if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float, 3>, dim3(B * nsplit), dim3(thr), smem, st, a);
+  else if (dtype == B200_DT_BF16)
+    le = deep ? b200_launch_pdl(gn_apply_kernel<bf16, 4>, dim3(B * nsplit), dim3(thr), smem, st, a)
+              : b200_launch_pdl(gn_apply_kernel<bf16, 3>, dim3(B * nsplit), dim3(thr), smem, st, a);
   else return B200_ERR_ARG;
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();

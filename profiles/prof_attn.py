@@ -10,10 +10,11 @@ for B in (128, 1024):
     qkv = torch.randn(B, L, 3 * C, device=dev).to(torch.bfloat16)
     out = torch.empty(B, L, C, device=dev, dtype=torch.bfloat16)
     run = lambda: _lib.check(lib.b200_attention_tc(_lib.ptr(qkv), _lib.ptr(out), B, L, C, C ** -0.5, _lib.stream()), "attn")
-    for _ in range(5): run()
+    REPS = int(os.environ.get('REPS', '50'))
+    for _ in range(5 if REPS > 1 else 0): run()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    n = 50
+    n = REPS
     e0.record()
     for _ in range(n): run()
     e1.record(); torch.cuda.synchronize()
