@@ -76,6 +76,13 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 // 8-wide vector of T (16 B for bf16, 32 B for fp32) as floats.
 template <typename T> struct Vec8;
 template <> struct Vec8<float> {
+  struct raw_t { float4 a, b; };
+  static __device__ __forceinline__ raw_t load_raw(const float* p) {
+    raw_t r; r.a = *reinterpret_cast<const float4*>(p); r.b = *reinterpret_cast<const float4*>(p + 4); return r;
+  }
+  static __device__ __forceinline__ void unpack(const raw_t& r, float* v) {
+    v[0] = r.a.x; v[1] = r.a.y; v[2] = r.a.z; v[3] = r.a.w; v[4] = r.b.x; v[5] = r.b.y; v[6] = r.b.z; v[7] = r.b.w;
+  }
   static __device__ __forceinline__ void load(const float* p, float* v) {
     float4 a = *reinterpret_cast<const float4*>(p);
     float4 b = *reinterpret_cast<const float4*>(p + 4);
@@ -87,6 +94,16 @@ template <> struct Vec8<float> {
   }
 };
 template <> struct Vec8<bf16> {
+  typedef uint4 raw_t;                       // as loaded: conversion can wait until the value is needed (registers)
+  static __device__ __forceinline__ raw_t load_raw(const bf16* p) { return *reinterpret_cast<const uint4*>(p); }
+  static __device__ __forceinline__ void unpack(const raw_t& r, float* v) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 f = __bfloat1622float2(h[i]);
+      v[2 * i] = f.x; v[2 * i + 1] = f.y;
+    }
+  }
   static __device__ __forceinline__ void load(const bf16* p, float* v) {
     uint4 r = *reinterpret_cast<const uint4*>(p);
     const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);

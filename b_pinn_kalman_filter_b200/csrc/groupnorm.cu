@@ -79,10 +79,10 @@ __global__ void __launch_bounds__(256) gn_partial_kernel(GnArgs a) {
   }
 }
 
-// MINB: resident blocks per SM the compiler must allow.  4 (64 registers, a few spilled words in the statistics fold)
-// when the launch is several waves deep -- 1024 one-image blocks stream 4-5 % faster with a fourth block per SM (ncu: 79
-// registers = 3 blocks = 31 % warps active before) -- and 3 (79 registers, no spills) for launches of at most one wave,
-// where the fold's latency is the time and the spills cost 9 % (profiles/r02p_gn_small_images.txt).
+// MINB: resident blocks per SM the compiler must allow.  The kernel is a stream, and what it lacked was warps (ncu: 79
+// registers = 3 blocks = 31 % warps active, 5.2 TB/s): the four loads in flight stay as loaded and are converted one at a
+// time, which brings the bf16 kernel to 64 registers without a spill = 4 blocks per SM (32x32x128: 101.8 -> 96.3 us at
+// 1024 images, 12.6 -> 11.3 us = 6.0 TB/s at 128).  A fifth block (48 registers) measured slightly worse again (98.2 us).
 template <typename T, int MINB>
 __global__ void __launch_bounds__(256, MINB) gn_apply_kernel(GnArgs a) {
   extern __shared__ float sh[];  // [G] mean, [G] rstd
@@ -149,17 +149,20 @@ __global__ void __launch_bounds__(256, MINB) gn_apply_kernel(GnArgs a) {
   T* dst = (T*)a.out + (size_t)b * a.HW * C + c0;
   int p = p_begin + pl;
   for (; p + 3 * ppt < p_end; p += 4 * ppt) {
-    float v[4][8];
+    // four loads in flight, kept as loaded; each is converted only when its turn comes (32 fewer live registers)
+    typename Vec8<T>::raw_t raw[4];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) Vec8<T>::load(src + (size_t)(p + u * ppt) * cs, v[u]);
+    for (int u = 0; u < 4; ++u) raw[u] = Vec8<T>::load_raw(src + (size_t)(p + u * ppt) * cs);
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
+      float v[8];
+      Vec8<T>::unpack(raw[u], v);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        float y = fmaf(v[u][j], sc[j], sf[j]);
-        v[u][j] = a.act ? silu_t<T>(y) : y;
+        float y = fmaf(v[j], sc[j], sf[j]);
+        v[j] = a.act ? silu_t<T>(y) : y;
       }
-      Vec8<T>::store(dst + (size_t)(p + u * ppt) * C, v[u]);
+      Vec8<T>::store(dst + (size_t)(p + u * ppt) * C, v);
     }
   }
   for (; p < p_end; p += ppt) {
@@ -441,11 +444,8 @@ extern "C" int b200_gn_apply(const void* x1, int C1, const void* x2, int C2, int
   if (G % 2) return B200_ERR_UNSUPPORTED;              // keeps the double scratch 8-byte aligned
   const size_t smem = 2 * G * sizeof(float) + 2 * C * sizeof(double);
   cudaError_t le;
-  const bool deep = (long long)B * nsplit > (long long)B200_NUM_SMS * 4;      // more than one wave even at 4 blocks per SM
   if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float, 3>, dim3(B * nsplit), dim3(thr), smem, st, a);
-  else if (dtype == B200_DT_BF16)
-    le = deep ? b200_launch_pdl(gn_apply_kernel<bf16, 4>, dim3(B * nsplit), dim3(thr), smem, st, a)
-              : b200_launch_pdl(gn_apply_kernel<bf16, 3>, dim3(B * nsplit), dim3(thr), smem, st, a);
+  else if (dtype == B200_DT_BF16) le = b200_launch_pdl(gn_apply_kernel<bf16, 4>, dim3(B * nsplit), dim3(thr), smem, st, a);
   else return B200_ERR_ARG;
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
@@ -484,11 +484,8 @@ extern "C" int b200_gn_apply_stats(const void* x1, int C1, const float* st1, int
     B200_RETURN_LAST();
   }
   const size_t smem = 2 * G * sizeof(float) + 2 * C * sizeof(double);
-  const bool deep = (long long)B * nsplit > (long long)B200_NUM_SMS * 4;      // more than one wave even at 4 blocks per SM
   if (dtype == B200_DT_F32) le = b200_launch_pdl(gn_apply_kernel<float, 3>, dim3(B * nsplit), dim3(thr), smem, st, a);
-  else if (dtype == B200_DT_BF16)
-    le = deep ? b200_launch_pdl(gn_apply_kernel<bf16, 4>, dim3(B * nsplit), dim3(thr), smem, st, a)
-              : b200_launch_pdl(gn_apply_kernel<bf16, 3>, dim3(B * nsplit), dim3(thr), smem, st, a);
+  else if (dtype == B200_DT_BF16) le = b200_launch_pdl(gn_apply_kernel<bf16, 4>, dim3(B * nsplit), dim3(thr), smem, st, a);
   else return B200_ERR_ARG;
   if (le != cudaSuccess) return -(1000 + (int)le);
   B200_RETURN_LAST();
