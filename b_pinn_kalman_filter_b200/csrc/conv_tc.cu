@@ -1166,7 +1166,22 @@ static int conv2d_tc_impl(const void* x1, int C1, const void* x2, int C2, const 
   else a2 = a1;
   rc = weight_map(&wm, w, Cout, Ktot, BN);          // rows beyond Cout are zero-filled by TMA (head: 3 of 16)
   if (rc) return rc;
-  if (out_mode != 0) return launch<16, 1>(a1, a2, wm, a1, p, st);
+  if (out_mode != 0) {
+    // network head / image-pyramid outputs (16-wide tiles): purely a data-movement launch, and with one box per tap every
+    // activation tile lands nine times in shared memory (250 us at B = 1024 for 268 MB of input).  Same halo loader as the
+    // wide variants when the geometry allows: three column-shifted boxes per K block serve all nine taps.
+    static const bool head_halo = [] { const char* e = getenv("B200_CONV_HEAD_HALO"); return !(e && e[0] == '0'); }();
+    if (head_halo && ksize == 3 && p.TB == 1 && H % HALO_TH == 0 && W % HALO_TW == 0 && halo_enabled() && !xmp) {
+      p.TW = HALO_TW; p.TH = HALO_TH; p.tiles_w = W / HALO_TW; p.tiles_h = H / HALO_TH;
+      p.num_m = B * p.tiles_w * p.tiles_h;
+      rc = act_map(&a1, x1, B, H, W, C1, HALO_TW, HALO_TH + 2, 1);
+      if (rc) return rc;
+      if (C2 > 0) { rc = act_map(&a2, x2, B, H, W, C2, HALO_TW, HALO_TH + 2, 1); if (rc) return rc; }
+      else a2 = a1;
+      return launch<16, 1, true>(a1, a2, wm, a1, p, st);
+    }
+    return launch<16, 1>(a1, a2, wm, a1, p, st);
+  }
   CUtensorMap om;
   static const bool hp256 = [] { const char* e = getenv("B200_CONV_HALO_PAIR256"); return !(e && e[0] == '0'); }();
   const bool halo256 = BN == 256 && hp256 && halo_pair_enabled() && pair_enabled();
